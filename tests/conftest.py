@@ -1,0 +1,29 @@
+import json
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "downloader-go_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def golden():
+    with open(os.path.join(ROOT, "tests", "golden", "vectors.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
+def gh():
+    """The product library through its ctypes mirror; GPU tests only. Fails loudly without a GPU."""
+    import gpuhash
+    ctx = gpuhash.Context()
+    yield ctx
+    ctx.close()
