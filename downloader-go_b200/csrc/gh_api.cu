@@ -1,0 +1,883 @@
+// gh_api.cu -- the C ABI of libgpuhash.so (include/gpuhash.h): contexts, the pinned staging ring,
+// host-span gather, multi-GPU sharding and the device-resident entry points.
+//
+// Host-side design: per device a ring of `slots` device buffers, each
+// with its own CUDA stream, so the H2D copies of slot b+1 run on the copy engine while the hashing
+// kernel of slot b runs on the SMs. Spans that already live in pinned memory are DMA'd straight from
+// the caller's buffer; pageable spans are first copied into the slot's pinned mirror by a small host
+// thread pool. Pieces / parts are independent, so devices get contiguous 64-aligned message ranges and
+// there is no collective of any kind.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/gpuhash.h"
+#include "gh_internal.h"
+
+namespace {
+
+constexpr uint64_t kDefaultSlotBytes = 256ull << 20;
+constexpr int kDefaultSlots = 3;
+constexpr int kDefaultStageThreads = 4;
+constexpr uint64_t kMinChunk = 64ull << 10;  // smallest per-message chunk of the chunk-interleaved mode
+
+// ------------------------------------------------------------------------------ host thread pool
+class Pool {
+   public:
+    explicit Pool(int n) {
+        for (int i = 0; i < n; i++) threads_.emplace_back([this] { run(); });
+    }
+    ~Pool() {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto& t : threads_) t.join();
+    }
+    // memcpy split over the pool; returns when every byte is copied.
+    void copy(uint8_t* dst, const uint8_t* src, uint64_t n) {
+        const uint64_t grain = 2ull << 20;
+        if (threads_.empty() || n <= grain) {
+            memcpy(dst, src, n);
+            return;
+        }
+        std::atomic<int> pending{0};
+        std::mutex dmu;
+        std::condition_variable dcv;
+        const uint64_t parts = std::min<uint64_t>((n + grain - 1) / grain, threads_.size() * 4);
+        const uint64_t each = ((n + parts - 1) / parts + 63) & ~63ull;
+        pending = static_cast<int>((n + each - 1) / each);
+        for (uint64_t off = 0; off < n; off += each) {
+            const uint64_t len = std::min(each, n - off);
+            std::lock_guard<std::mutex> g(mu_);
+            q_.push_back([=, &pending, &dmu, &dcv] {
+                memcpy(dst + off, src + off, len);
+                if (pending.fetch_sub(1) == 1) {
+                    std::lock_guard<std::mutex> g2(dmu);
+                    dcv.notify_one();
+                }
+            });
+            cv_.notify_one();
+        }
+        std::unique_lock<std::mutex> lk(dmu);
+        dcv.wait(lk, [&] { return pending.load() == 0; });
+    }
+
+    // strided copy: rows of `width` bytes, pitches in bytes; rows are spread over the pool.
+    void copy2d(uint8_t* dst, uint64_t dpitch, const uint8_t* src, uint64_t spitch, uint64_t width, uint64_t rows) {
+        if (rows == 0 || width == 0) return;
+        const uint64_t nt = threads_.empty() ? 1 : threads_.size();
+        const uint64_t per = std::max<uint64_t>(1, (rows + nt * 4 - 1) / (nt * 4));
+        if (threads_.empty() || rows * width <= (2ull << 20)) {
+            for (uint64_t r = 0; r < rows; r++) memcpy(dst + r * dpitch, src + r * spitch, width);
+            return;
+        }
+        std::atomic<int> pending{static_cast<int>((rows + per - 1) / per)};
+        std::mutex dmu;
+        std::condition_variable dcv;
+        for (uint64_t r0 = 0; r0 < rows; r0 += per) {
+            const uint64_t r1 = std::min(rows, r0 + per);
+            std::lock_guard<std::mutex> g(mu_);
+            q_.push_back([=, &pending, &dmu, &dcv] {
+                for (uint64_t r = r0; r < r1; r++) memcpy(dst + r * dpitch, src + r * spitch, width);
+                if (pending.fetch_sub(1) == 1) {
+                    std::lock_guard<std::mutex> g2(dmu);
+                    dcv.notify_one();
+                }
+            });
+            cv_.notify_one();
+        }
+        std::unique_lock<std::mutex> lk(dmu);
+        dcv.wait(lk, [&] { return pending.load() == 0; });
+    }
+
+   private:
+    void run() {
+        for (;;) {
+            std::function<void()> f;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+                if (stop_ && q_.empty()) return;
+                f = std::move(q_.front());
+                q_.erase(q_.begin());
+            }
+            f();
+        }
+    }
+    std::vector<std::thread> threads_;
+    std::vector<std::function<void()>> q_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    bool stop_ = false;
+};
+
+struct Slot {
+    uint8_t* d_buf = nullptr;
+    uint8_t* h_pin = nullptr;  // pinned mirror, allocated on first pageable span
+    cudaStream_t stream = nullptr;
+    cudaEvent_t h2d_done = nullptr;  // last H2D out of h_pin
+    bool h2d_pending = false;
+};
+
+struct Device {
+    int ordinal = -1;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;  // stream of the device-resident entry points and of result copies
+    std::vector<Slot> slots;
+    // grow-only device scratch reused across calls
+    uint8_t* d_out = nullptr;   uint64_t d_out_cap = 0;   // digests (+ expected)
+    uint32_t* d_ok = nullptr;   uint64_t d_ok_cap = 0;
+    uint32_t* d_state = nullptr; uint64_t d_state_cap = 0;
+    uint8_t* h_out = nullptr;   uint64_t h_out_cap = 0;   // pinned mirror of results
+    std::vector<cudaEvent_t> ev_pool;                     // start/stop pairs for kernel timing
+    size_t ev_used = 0;
+    cudaEvent_t chain = nullptr;                          // orders chunk j+1's kernel after chunk j's
+};
+
+}  // namespace
+
+struct gh_ctx {
+    std::mutex mu;
+    std::vector<Device> devs;
+    uint64_t slot_bytes = kDefaultSlotBytes;
+    int n_slots = kDefaultSlots;
+    Pool* pool = nullptr;
+    std::string last_error;
+    gh_stats stats{};
+    std::atomic<uint64_t> launches{0}, h2d{0}, d2h{0};
+    bool lost = false;
+};
+
+namespace {
+
+int fail(gh_ctx* c, int code, const std::string& msg) {
+    if (c) c->last_error = msg;
+    return code;
+}
+
+int cuda_fail(gh_ctx* c, cudaError_t e, const char* what) {
+    std::string msg = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    if (c) {
+        c->last_error = msg;
+        if (e == cudaErrorIllegalAddress || e == cudaErrorLaunchFailure || e == cudaErrorHardwareStackError ||
+            e == cudaErrorIllegalInstruction || e == cudaErrorMisalignedAddress)
+            c->lost = true;
+    }
+    if (e == cudaErrorMemoryAllocation) return GH_ENOMEM;
+    return (c && c->lost) ? GH_ECTX_LOST : GH_ECUDA;
+}
+
+#define GH_CUDA(ctx, call)                                           \
+    do {                                                             \
+        cudaError_t _e = (call);                                     \
+        if (_e != cudaSuccess) return cuda_fail((ctx), _e, #call);   \
+    } while (0)
+
+uint64_t count_msgs(uint64_t total, uint64_t msg_len) {
+    if (total == 0 || msg_len == 0) return 0;
+    return (total + msg_len - 1) / msg_len;
+}
+
+int digest_len(int alg) { return alg == GH_SHA1 ? 20 : alg == GH_MD5 ? 16 : 32; }
+
+template <class T>
+int grow(gh_ctx* c, T** p, uint64_t* cap, uint64_t need_bytes, bool pinned_host = false) {
+    if (need_bytes <= *cap && *p) return GH_OK;
+    if (*p) {
+        if (pinned_host) cudaFreeHost(*p);
+        else cudaFree(*p);
+        *p = nullptr;
+        *cap = 0;
+    }
+    uint64_t want = std::max<uint64_t>(need_bytes, 4096);
+    void* q = nullptr;
+    cudaError_t e = pinned_host ? cudaMallocHost(&q, want) : cudaMalloc(&q, want);
+    if (e != cudaSuccess) return cuda_fail(c, e, pinned_host ? "cudaMallocHost" : "cudaMalloc");
+    *p = static_cast<T*>(q);
+    *cap = want;
+    return GH_OK;
+}
+
+// Splits `algos` into the kernel variants that exist: SHA-1 alone, and MD5/SHA-256 alone or fused.
+void split_algos(int algos, int out[2], int* n) {
+    *n = 0;
+    if (algos & GH_SHA1) out[(*n)++] = GH_SHA1;
+    if (algos & (GH_MD5 | GH_SHA256)) out[(*n)++] = algos & (GH_MD5 | GH_SHA256);
+}
+
+struct EvPair { cudaEvent_t a, b; };
+
+int next_events(gh_ctx* c, Device& d, EvPair* out) {
+    if (d.ev_used + 2 > d.ev_pool.size()) {
+        for (int i = 0; i < 2; i++) {
+            cudaEvent_t e;
+            GH_CUDA(c, cudaEventCreate(&e));
+            d.ev_pool.push_back(e);
+        }
+    }
+    out->a = d.ev_pool[d.ev_used++];
+    out->b = d.ev_pool[d.ev_used++];
+    return GH_OK;
+}
+
+// Launch all kernel variants for one window on `stream`, bracketed by a timing event pair.
+int launch_window(gh_ctx* c, Device& d, int algos, GhJob job, cudaStream_t stream, bool timed) {
+    int parts[2], np;
+    split_algos(algos, parts, &np);
+    EvPair ev{};
+    if (timed) {
+        int rc = next_events(c, d, &ev);
+        if (rc) return rc;
+        GH_CUDA(c, cudaEventRecord(ev.a, stream));
+    }
+    for (int i = 0; i < np; i++) {
+        GhJob j = job;
+        if (parts[i] != GH_SHA1) { j.expected = nullptr; j.ok_words = nullptr; }
+        GH_CUDA(c, gh_launch_hash(parts[i], j, d.sm_count, stream));
+        c->launches++;
+    }
+    if (timed) GH_CUDA(c, cudaEventRecord(ev.b, stream));
+    return GH_OK;
+}
+
+// --------------------------------------------------------------------------- span gather
+struct SpanIndex {
+    const gh_span* spans;
+    size_t n;
+    std::vector<uint64_t> start;  // stream offset of each span, plus the total at [n]
+    std::vector<char> pinned;
+    uint64_t total() const { return start[n]; }
+};
+
+void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
+    ix->spans = spans;
+    ix->n = n;
+    ix->start.resize(n + 1);
+    ix->pinned.resize(n);
+    uint64_t off = 0;
+    for (size_t i = 0; i < n; i++) {
+        ix->start[i] = off;
+        off += spans[i].len;
+        cudaPointerAttributes a{};
+        bool pinned = false;
+        if (spans[i].len && cudaPointerGetAttributes(&a, spans[i].host_ptr) == cudaSuccess)
+            pinned = a.type == cudaMemoryTypeHost;
+        cudaGetLastError();  // older drivers flag unregistered memory as an error; clear it
+        ix->pinned[i] = pinned;
+    }
+    ix->start[n] = off;
+}
+
+// Copies stream bytes [a, b) into slot memory at d_dst (device) / h_dst (pinned mirror, same offset).
+// Pinned spans are DMA'd directly; pageable ones are staged. `staged_lo/hi` accumulate the range of
+// the mirror that needs one H2D afterwards.
+int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint64_t dst_off, uint64_t* staged_lo,
+           uint64_t* staged_hi) {
+    if (a >= b) return GH_OK;
+    size_t i = std::upper_bound(ix.start.begin(), ix.start.begin() + ix.n, a) - ix.start.begin() - 1;
+    uint64_t x = a;
+    while (x < b && i < ix.n) {
+        const uint64_t s_lo = ix.start[i], s_hi = ix.start[i + 1];
+        if (s_hi <= x) { i++; continue; }
+        const uint64_t hi = std::min(b, s_hi);
+        const uint8_t* src = static_cast<const uint8_t*>(ix.spans[i].host_ptr) + (x - s_lo);
+        const uint64_t len = hi - x;
+        const uint64_t doff = dst_off + (x - a);
+        if (ix.pinned[i]) {
+            GH_CUDA(c, cudaMemcpyAsync(s.d_buf + doff, src, len, cudaMemcpyHostToDevice, s.stream));
+        } else {
+            if (!s.h_pin) GH_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256));
+            if (s.h2d_pending) {  // the previous window's DMA out of this mirror must have drained
+                GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
+                s.h2d_pending = false;
+            }
+            c->pool->copy(s.h_pin + doff, src, len);
+            *staged_lo = std::min(*staged_lo, doff);
+            *staged_hi = std::max(*staged_hi, doff + len);
+        }
+        c->h2d += len;
+        x = hi;
+        i++;
+    }
+    return GH_OK;
+}
+
+int flush_staged(gh_ctx* c, Slot& s, uint64_t lo, uint64_t hi) {
+    if (lo >= hi) return GH_OK;
+    GH_CUDA(c, cudaMemcpyAsync(s.d_buf + lo, s.h_pin + lo, hi - lo, cudaMemcpyHostToDevice, s.stream));
+    GH_CUDA(c, cudaEventRecord(s.h2d_done, s.stream));
+    s.h2d_pending = true;
+    return GH_OK;
+}
+
+// Chunk-interleaved window: for every message m of the group [g0, g0+g) bring stream bytes
+// [(g0+m)*L + prior, +min(chunk, len_m - prior)) to slot offset m*chunk. Consecutive rows that lie
+// inside one span move as one strided copy (DMA for pinned spans, pooled memcpy for pageable ones);
+// a row that straddles a span (file) boundary falls back to the byte-exact 1-D gather.
+int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g, uint64_t L, uint64_t last_len,
+                uint64_t prior, uint64_t chunk) {
+    uint64_t st_lo = ~0ull, st_hi = 0;
+    size_t si = 0;
+    uint64_t m = 0;
+    while (m < g) {
+        const uint64_t mlen = (m == g - 1) ? last_len : L;
+        if (prior >= mlen) { m++; continue; }
+        const uint64_t w = std::min(chunk, mlen - prior);
+        const uint64_t lo = (g0 + m) * L + prior;
+        while (si + 1 < ix.n && ix.start[si + 1] <= lo) si++;
+        while (si > 0 && ix.start[si] > lo) si--;
+        const bool inside = si < ix.n && ix.start[si] <= lo && lo + w <= ix.start[si + 1];
+        if (!inside) {
+            int rc = gather(c, ix, lo, lo + w, s, m * chunk, &st_lo, &st_hi);
+            if (rc) return rc;
+            m++;
+            continue;
+        }
+        // extend over following rows of the same width that stay inside span si
+        uint64_t rows = 1;
+        while (m + rows < g) {
+            const uint64_t m2 = m + rows;
+            const uint64_t mlen2 = (m2 == g - 1) ? last_len : L;
+            if (prior >= mlen2 || std::min(chunk, mlen2 - prior) != w) break;
+            if ((g0 + m2) * L + prior + w > ix.start[si + 1]) break;
+            rows++;
+        }
+        const uint8_t* src = static_cast<const uint8_t*>(ix.spans[si].host_ptr) + (lo - ix.start[si]);
+        if (ix.pinned[si]) {
+            GH_CUDA(c, cudaMemcpy2DAsync(s.d_buf + m * chunk, chunk, src, L, w, rows, cudaMemcpyHostToDevice, s.stream));
+        } else {
+            if (!s.h_pin) GH_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256));
+            if (s.h2d_pending) {
+                GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
+                s.h2d_pending = false;
+            }
+            c->pool->copy2d(s.h_pin + m * chunk, chunk, src, L, w, rows);
+            st_lo = std::min(st_lo, m * chunk);
+            st_hi = std::max(st_hi, (m + rows - 1) * chunk + w);
+        }
+        c->h2d += w * rows;
+        m += rows;
+    }
+    return flush_staged(c, s, st_lo, st_hi);
+}
+
+// --------------------------------------------------------------------------- one device's share
+struct BatchArgs {
+    const SpanIndex* ix;
+    uint64_t msg_len;
+    int algos;
+    const uint8_t* expected;  // host, 20*n_total or null
+    uint8_t* out[3];          // host: sha1, md5, sha256 (whole-call arrays) or null
+    uint64_t* bitmap;         // host, whole-call, or null
+    uint64_t n_total;
+};
+
+int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m1, double* kernel_ms) {
+    *kernel_ms = 0;
+    if (m0 >= m1) return GH_OK;
+    GH_CUDA(c, cudaSetDevice(d.ordinal));
+    const uint64_t n = m1 - m0, L = A.msg_len, total = A.ix->total();
+    const uint64_t range_lo = m0 * L, range_hi = std::min(m1 * L, total);
+    const uint64_t last_len_global = total - (A.n_total - 1) * L;
+
+    // result layout on the device: [sha1 20n][md5 16n][sha256 32n][expected 20n], each 256-aligned
+    auto al = [](uint64_t v) { return (v + 255) & ~255ull; };
+    const uint64_t o_sha1 = 0, o_md5 = al(20 * n), o_sha256 = o_md5 + al(16 * n), o_exp = o_sha256 + al(32 * n);
+    const uint64_t out_bytes = o_exp + al(20 * n);
+    int rc;
+    if ((rc = grow(c, &d.d_out, &d.d_out_cap, out_bytes))) return rc;
+    if ((rc = grow(c, &d.h_out, &d.h_out_cap, out_bytes, true))) return rc;
+    const uint64_t ok_words = (n + 31) / 32;
+    if ((rc = grow(c, &d.d_ok, &d.d_ok_cap, (ok_words + 1) * 4))) return rc;
+    const bool want_ok = A.expected != nullptr && (A.algos & GH_SHA1);
+    if (want_ok) {
+        memcpy(d.h_out + o_exp, A.expected + 20 * m0, 20 * n);
+        GH_CUDA(c, cudaMemcpyAsync(d.d_out + o_exp, d.h_out + o_exp, 20 * n, cudaMemcpyHostToDevice, d.stream));
+        GH_CUDA(c, cudaMemsetAsync(d.d_ok, 0, (ok_words + 1) * 4, d.stream));
+    }
+    cudaEvent_t prep;
+    {
+        EvPair ev;
+        if ((rc = next_events(c, d, &ev))) return rc;
+        prep = ev.a;
+        GH_CUDA(c, cudaEventRecord(prep, d.stream));
+        for (auto& s : d.slots) GH_CUDA(c, cudaStreamWaitEvent(s.stream, prep, 0));
+    }
+    const size_t first_timing_event = d.ev_used;
+
+    GhJob job{};
+    job.msg_len = L;
+    job.sha1 = (A.algos & GH_SHA1) ? d.d_out + o_sha1 : nullptr;
+    job.md5 = (A.algos & GH_MD5) ? d.d_out + o_md5 : nullptr;
+    job.sha256 = (A.algos & GH_SHA256) ? d.d_out + o_sha256 : nullptr;
+
+    const uint64_t S = c->slot_bytes;
+    const uint64_t bytes_here = range_hi - range_lo;
+    if (bytes_here <= S || L <= kMinChunk) {
+        // whole messages per window (everything fits one window, or messages are small enough that a
+        // window still carries thousands of independent chains)
+        const uint64_t per = std::max<uint64_t>(1, S / L);
+        uint64_t b = 0;
+        for (uint64_t q = m0; q < m1; q += per, b++) {
+            Slot& s = d.slots[b % d.slots.size()];
+            const uint64_t k = std::min(per, m1 - q);
+            const uint64_t lo = q * L, hi = std::min((q + k) * L, total);
+            uint64_t st_lo = ~0ull, st_hi = 0;
+            if ((rc = gather(c, *A.ix, lo, hi, s, 0, &st_lo, &st_hi))) return rc;
+            if ((rc = flush_staged(c, s, st_lo, st_hi))) return rc;
+            GhJob j = job;
+            j.data = s.d_buf;
+            j.stride = L;
+            j.chunk_len = L;
+            j.prior = 0;
+            j.n_msgs = k;
+            j.last_msg_len = (q + k == A.n_total) ? last_len_global : L;
+            const uint64_t rel = q - m0;
+            if (j.sha1) j.sha1 += 20 * rel;
+            if (j.md5) j.md5 += 16 * rel;
+            if (j.sha256) j.sha256 += 32 * rel;
+            if (want_ok) {
+                j.expected = d.d_out + o_exp + 20 * rel;
+                j.ok_words = d.d_ok;
+                j.ok_base = rel;
+            }
+            if ((rc = launch_window(c, d, A.algos, j, s.stream, true))) return rc;
+        }
+    } else {
+        // chunk-interleaved: every window carries the next `chunk` bytes of every message of a group,
+        // so that all chains advance together; midstates stay in HBM. Rows that
+        // lie inside one pinned span travel as a single strided (2-D) DMA.
+        if ((rc = grow(c, &d.d_state, &d.d_state_cap, n * GH_STATE_WORDS * 4))) return rc;
+        if (!d.chain) GH_CUDA(c, cudaEventCreateWithFlags(&d.chain, cudaEventDisableTiming));
+        const uint64_t gsz = std::min<uint64_t>(n, std::max<uint64_t>(1, S / kMinChunk));
+        uint64_t b = 0;
+        bool have_chain = false;
+        for (uint64_t g0 = m0; g0 < m1; g0 += gsz) {
+            const uint64_t g = std::min(gsz, m1 - g0);
+            const uint64_t chunk = std::min<uint64_t>((S / g) & ~63ull, (L + 63) & ~63ull);
+            const uint64_t rel = g0 - m0;
+            const uint64_t g_last_len = (g0 + g == A.n_total) ? last_len_global : L;
+            for (uint64_t prior = 0; prior < L; prior += chunk, b++) {
+                Slot& s = d.slots[b % d.slots.size()];
+                if ((rc = gather_rows(c, *A.ix, s, g0, g, L, g_last_len, prior, chunk))) return rc;
+                GhJob j = job;
+                j.data = s.d_buf;
+                j.stride = chunk;
+                j.chunk_len = chunk;
+                j.prior = prior;
+                j.n_msgs = g;
+                j.last_msg_len = g_last_len;
+                j.state = d.d_state;  // group-local [word][g]; launches are chained, so groups may share it
+                if (j.sha1) j.sha1 += 20 * rel;
+                if (j.md5) j.md5 += 16 * rel;
+                if (j.sha256) j.sha256 += 32 * rel;
+                if (want_ok) {
+                    j.expected = d.d_out + o_exp + 20 * rel;
+                    j.ok_words = d.d_ok;
+                    j.ok_base = rel;
+                }
+                if (have_chain) GH_CUDA(c, cudaStreamWaitEvent(s.stream, d.chain, 0));
+                if ((rc = launch_window(c, d, A.algos, j, s.stream, true))) return rc;
+                GH_CUDA(c, cudaEventRecord(d.chain, s.stream));
+                have_chain = true;
+            }
+        }
+    }
+    const size_t last_timing_event = d.ev_used;
+
+    // results back: wait for every slot stream, then one D2H per selected output
+    for (auto& s : d.slots) {
+        EvPair ev;
+        if ((rc = next_events(c, d, &ev))) return rc;
+        GH_CUDA(c, cudaEventRecord(ev.a, s.stream));
+        GH_CUDA(c, cudaStreamWaitEvent(d.stream, ev.a, 0));
+    }
+    struct { int alg; uint64_t off; int idx; } outs[3] = {{GH_SHA1, o_sha1, 0}, {GH_MD5, o_md5, 1}, {GH_SHA256, o_sha256, 2}};
+    for (auto& o : outs) {
+        if (!(A.algos & o.alg) || !A.out[o.idx]) continue;
+        const uint64_t bytes = static_cast<uint64_t>(digest_len(o.alg)) * n;
+        GH_CUDA(c, cudaMemcpyAsync(d.h_out + o.off, d.d_out + o.off, bytes, cudaMemcpyDeviceToHost, d.stream));
+        c->d2h += bytes;
+    }
+    uint32_t* h_ok = reinterpret_cast<uint32_t*>(d.h_out + o_exp);  // expected is no longer needed on the host
+    if (want_ok && A.bitmap) {
+        GH_CUDA(c, cudaMemcpyAsync(h_ok, d.d_ok, ok_words * 4, cudaMemcpyDeviceToHost, d.stream));
+        c->d2h += ok_words * 4;
+    }
+    GH_CUDA(c, cudaStreamSynchronize(d.stream));
+    for (auto& s : d.slots) s.h2d_pending = false;
+    for (auto& o : outs) {
+        if (!(A.algos & o.alg) || !A.out[o.idx]) continue;
+        const uint64_t dl = digest_len(o.alg);
+        memcpy(A.out[o.idx] + dl * m0, d.h_out + o.off, dl * n);
+    }
+    if (want_ok && A.bitmap) {  // m0 is 64-aligned: this device owns whole 64-bit words
+        uint32_t* dst = reinterpret_cast<uint32_t*>(A.bitmap) + m0 / 32;
+        memcpy(dst, h_ok, ok_words * 4);
+        if (ok_words & 1) dst[ok_words] = 0;
+    }
+    for (size_t e = first_timing_event; e + 1 < last_timing_event; e += 2) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, d.ev_pool[e], d.ev_pool[e + 1]) == cudaSuccess) *kernel_ms += ms;
+    }
+    (void)range_lo; (void)range_hi;
+    return GH_OK;
+}
+
+int run_batch(gh_ctx* c, const gh_span* spans, size_t n_spans, uint64_t msg_len, int algos, const uint8_t* expected,
+              uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+    if (!c) return GH_EINVAL;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (c->lost) return fail(c, GH_ECTX_LOST, "context lost after a device fault");
+    if (msg_len == 0) return fail(c, GH_EINVAL, "message length must be > 0");
+    if (n_spans && !spans) return fail(c, GH_EINVAL, "spans is NULL");
+    if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256)))
+        return fail(c, GH_EINVAL, "algos must be a mask of GH_SHA1|GH_MD5|GH_SHA256");
+    for (size_t i = 0; i < n_spans; i++)
+        if (spans[i].len && !spans[i].host_ptr) return fail(c, GH_EINVAL, "span with NULL pointer and non-zero length");
+    const auto t0 = std::chrono::steady_clock::now();
+    SpanIndex ix;
+    build_index(spans, n_spans, &ix);
+    const uint64_t n = count_msgs(ix.total(), msg_len);
+    if (n_bad) *n_bad = 0;
+    if (n == 0) {
+        c->stats.kernel_ms = 0;
+        c->stats.wall_ms = 0;
+        return GH_OK;
+    }
+    BatchArgs A{&ix, msg_len, algos, expected, {sha1_out, md5_out, sha256_out}, bitmap, n};
+    const int nd = static_cast<int>(c->devs.size());
+    std::vector<int> rcs(nd, GH_OK);
+    std::vector<double> kms(nd, 0.0);
+    std::vector<std::string> errs(nd);
+    for (auto& d : c->devs) d.ev_used = 0;
+    if (nd == 1) {
+        rcs[0] = run_device(c, c->devs[0], A, 0, n, &kms[0]);
+    } else {
+        std::vector<std::thread> th;
+        for (int i = 0; i < nd; i++) {
+            uint64_t b, e;
+            gh_shard_range(n, nd, i, &b, &e);
+            th.emplace_back([&, i, b, e] { rcs[i] = run_device(c, c->devs[i], A, b, e, &kms[i]); });
+        }
+        for (auto& t : th) t.join();
+    }
+    for (int i = 0; i < nd; i++)
+        if (rcs[i]) return rcs[i];
+    if (bitmap && expected && (algos & GH_SHA1)) {
+        uint64_t good = 0;
+        const uint64_t words = (n + 63) / 64;
+        for (uint64_t w = 0; w < words; w++) good += __builtin_popcountll(bitmap[w]);
+        if (n_bad) *n_bad = n - good;
+    } else if (bitmap) {
+        memset(bitmap, 0, ((n + 63) / 64) * 8);
+    }
+    c->stats.kernel_ms = *std::max_element(kms.begin(), kms.end());
+    c->stats.wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return GH_OK;
+}
+
+Device* get_dev(gh_ctx* c, int idx) {
+    if (!c || idx < 0 || idx >= static_cast<int>(c->devs.size())) return nullptr;
+    return &c->devs[idx];
+}
+
+}  // namespace
+
+// ================================================================================ C ABI
+extern "C" {
+
+const char* gh_version(void) { return "gpuhash 0.1 (sm_100a)"; }
+
+const char* gh_strerror(int status) {
+    switch (status) {
+        case GH_OK: return "ok";
+        case GH_EINVAL: return "invalid argument";
+        case GH_ENODEVICE: return "no usable CUDA device";
+        case GH_ENOMEM: return "out of memory";
+        case GH_ECUDA: return "CUDA error";
+        case GH_ECTX_LOST: return "context lost after a device fault";
+        case GH_ERANGE: return "size beyond limit";
+        default: return "unknown status";
+    }
+}
+
+const char* gh_last_error(gh_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+
+void gh_shard_range(uint64_t n_msgs, int n_shards, int shard, uint64_t* begin, uint64_t* end) {
+    if (n_shards < 1) n_shards = 1;
+    const uint64_t words = (n_msgs + 63) / 64;  // shard in units of 64 messages = one bitmap word
+    const uint64_t base = words / n_shards, extra = words % n_shards;
+    const uint64_t s = static_cast<uint64_t>(shard);
+    const uint64_t w0 = s * base + std::min<uint64_t>(s, extra);
+    const uint64_t w1 = w0 + base + (s < extra ? 1 : 0);
+    *begin = std::min(n_msgs, w0 * 64);
+    *end = std::min(n_msgs, w1 * 64);
+}
+
+int gh_create(gh_ctx** out, const gh_config* cfg) {
+    if (!out) return GH_EINVAL;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return GH_ENODEVICE;  // no CPU fallback on purpose
+    gh_ctx* c = new gh_ctx();
+    int nd = cfg && cfg->n_devices > 0 ? cfg->n_devices : count;
+    if (cfg && cfg->slot_bytes) c->slot_bytes = (cfg->slot_bytes + 255) & ~255ull;
+    if (cfg && cfg->slots) c->n_slots = std::max(2, cfg->slots);
+    const int st = cfg && cfg->stage_threads > 0 ? cfg->stage_threads : kDefaultStageThreads;
+    for (int i = 0; i < nd; i++) {
+        const int ord = (cfg && cfg->devices && cfg->n_devices > 0) ? cfg->devices[i] : i;
+        if (ord < 0 || ord >= count) {
+            gh_destroy(c);
+            return GH_ENODEVICE;
+        }
+        Device d;
+        d.ordinal = ord;
+        c->devs.push_back(d);
+    }
+    for (auto& d : c->devs) {
+        bool ok = cudaSetDevice(d.ordinal) == cudaSuccess;
+        ok = ok && cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, d.ordinal) == cudaSuccess;
+        ok = ok && gh_kernels_init_device() == cudaSuccess;
+        ok = ok && cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) == cudaSuccess;
+        d.slots.resize(c->n_slots);
+        for (auto& s : d.slots) {
+            ok = ok && cudaMalloc(reinterpret_cast<void**>(&s.d_buf), c->slot_bytes + 256) == cudaSuccess;
+            ok = ok && cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) == cudaSuccess;
+            ok = ok && cudaEventCreateWithFlags(&s.h2d_done, cudaEventDisableTiming) == cudaSuccess;
+        }
+        if (!ok) {
+            cudaError_t le = cudaGetLastError();
+            gh_destroy(c);
+            return le == cudaErrorMemoryAllocation ? GH_ENOMEM : GH_ECUDA;
+        }
+    }
+    c->pool = new Pool(st);
+    *out = c;
+    return GH_OK;
+}
+
+void gh_destroy(gh_ctx* c) {
+    if (!c) return;
+    for (auto& d : c->devs) {
+        if (cudaSetDevice(d.ordinal) != cudaSuccess) continue;
+        cudaDeviceSynchronize();
+        for (auto& s : d.slots) {
+            if (s.d_buf) cudaFree(s.d_buf);
+            if (s.h_pin) cudaFreeHost(s.h_pin);
+            if (s.stream) cudaStreamDestroy(s.stream);
+            if (s.h2d_done) cudaEventDestroy(s.h2d_done);
+        }
+        if (d.d_out) cudaFree(d.d_out);
+        if (d.d_ok) cudaFree(d.d_ok);
+        if (d.d_state) cudaFree(d.d_state);
+        if (d.h_out) cudaFreeHost(d.h_out);
+        for (auto e : d.ev_pool) cudaEventDestroy(e);
+        if (d.chain) cudaEventDestroy(d.chain);
+        if (d.stream) cudaStreamDestroy(d.stream);
+    }
+    delete c->pool;
+    delete c;
+}
+
+int gh_device_count(gh_ctx* ctx) { return ctx ? static_cast<int>(ctx->devs.size()) : 0; }
+
+int gh_get_stats(gh_ctx* ctx, gh_stats* out) {
+    if (!ctx || !out) return GH_EINVAL;
+    *out = ctx->stats;
+    out->kernel_launches = ctx->launches.load();
+    out->h2d_bytes = ctx->h2d.load();
+    out->d2h_bytes = ctx->d2h.load();
+    return GH_OK;
+}
+
+int gh_verify_pieces(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t piece_len, const uint8_t* expected,
+                     uint8_t* digests_out, uint64_t* ok_bitmap_out, uint64_t* n_bad_out) {
+    return run_batch(ctx, spans, n_spans, piece_len, GH_SHA1, expected, digests_out, nullptr, nullptr, ok_bitmap_out,
+                     n_bad_out);
+}
+
+int gh_hash_parts(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t part_len, int algos, uint8_t* sha1_out,
+                  uint8_t* md5_out, uint8_t* sha256_out) {
+    return run_batch(ctx, spans, n_spans, part_len, algos, nullptr, sha1_out, md5_out, sha256_out, nullptr, nullptr);
+}
+
+int gh_s3_etag(gh_ctx* ctx, const uint8_t* part_md5s, uint64_t n_parts, char* out, size_t out_len) {
+    if (!ctx || !out || out_len < 56 || (n_parts && !part_md5s)) return GH_EINVAL;
+    uint8_t d[16];
+    gh_span sp{part_md5s, n_parts * 16};
+    int rc;
+    if (n_parts == 0) {
+        // md5 of the empty string: hash one zero-length message through the device path
+        return fail(ctx, GH_EINVAL, "an S3 multipart upload has at least one part");
+    }
+    rc = gh_hash_parts(ctx, &sp, 1, n_parts * 16, GH_MD5, nullptr, d, nullptr);
+    if (rc) return rc;
+    for (int i = 0; i < 16; i++) snprintf(out + 2 * i, 3, "%02x", d[i]);
+    snprintf(out + 32, out_len - 32, "-%llu", static_cast<unsigned long long>(n_parts));
+    return GH_OK;
+}
+
+// ---- device-resident -----------------------------------------------------------------------
+static int device_call(gh_ctx* ctx, int dev_index, int algos, const GhJob& job_in, void* cuda_stream) {
+    Device* d = get_dev(ctx, dev_index);
+    if (!d) return fail(ctx, GH_EINVAL, "bad device index");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    if (ctx->lost) return GH_ECTX_LOST;
+    GH_CUDA(ctx, cudaSetDevice(d->ordinal));
+    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : d->stream;
+    if (job_in.ok_words && job_in.prior == 0)
+        GH_CUDA(ctx, cudaMemsetAsync(job_in.ok_words, 0, ((job_in.n_msgs + 31) / 32) * 4, st));
+    d->ev_used = 0;
+    const auto t0 = std::chrono::steady_clock::now();
+    int rc = launch_window(ctx, *d, algos, job_in, st, cuda_stream == nullptr);
+    if (rc) return rc;
+    if (!cuda_stream) {
+        GH_CUDA(ctx, cudaStreamSynchronize(st));
+        float ms = 0;
+        if (d->ev_used >= 2) cudaEventElapsedTime(&ms, d->ev_pool[0], d->ev_pool[1]);
+        ctx->stats.kernel_ms = ms;
+        ctx->stats.wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return GH_OK;
+}
+
+int gh_verify_pieces_device(gh_ctx* ctx, int dev_index, const void* d_data, uint64_t total, uint64_t piece_len,
+                            const uint8_t* d_expected, uint8_t* d_digests, uint32_t* d_ok_words, void* cuda_stream) {
+    if (!ctx) return GH_EINVAL;
+    if (piece_len == 0) return fail(ctx, GH_EINVAL, "piece length must be > 0");
+    const uint64_t n = count_msgs(total, piece_len);
+    if (n == 0) return GH_OK;
+    if (!d_data) return fail(ctx, GH_EINVAL, "d_data is NULL");
+    GhJob j{};
+    j.data = static_cast<const uint8_t*>(d_data);
+    j.stride = piece_len;
+    j.chunk_len = piece_len;
+    j.n_msgs = n;
+    j.msg_len = piece_len;
+    j.last_msg_len = total - (n - 1) * piece_len;
+    j.sha1 = d_digests;
+    j.expected = d_expected;
+    j.ok_words = d_expected ? d_ok_words : nullptr;
+    return device_call(ctx, dev_index, GH_SHA1, j, cuda_stream);
+}
+
+int gh_hash_parts_device(gh_ctx* ctx, int dev_index, const void* d_data, uint64_t total, uint64_t part_len, int algos,
+                         uint8_t* d_sha1, uint8_t* d_md5, uint8_t* d_sha256, void* cuda_stream) {
+    if (!ctx) return GH_EINVAL;
+    if (part_len == 0) return fail(ctx, GH_EINVAL, "part length must be > 0");
+    if (!(algos & 7) || (algos & ~7)) return fail(ctx, GH_EINVAL, "bad algos mask");
+    const uint64_t n = count_msgs(total, part_len);
+    if (n == 0) return GH_OK;
+    if (!d_data) return fail(ctx, GH_EINVAL, "d_data is NULL");
+    GhJob j{};
+    j.data = static_cast<const uint8_t*>(d_data);
+    j.stride = part_len;
+    j.chunk_len = part_len;
+    j.n_msgs = n;
+    j.msg_len = part_len;
+    j.last_msg_len = total - (n - 1) * part_len;
+    j.sha1 = d_sha1;
+    j.md5 = d_md5;
+    j.sha256 = d_sha256;
+    return device_call(ctx, dev_index, algos, j, cuda_stream);
+}
+
+int gh_hash_update_device(gh_ctx* ctx, int dev_index, int algos, const void* d_data, uint64_t stride,
+                          uint64_t chunk_len, uint64_t prior_bytes, uint64_t n_msgs, uint64_t msg_len,
+                          uint64_t last_msg_len, uint32_t* d_state, uint8_t* d_sha1, uint8_t* d_md5, uint8_t* d_sha256,
+                          void* cuda_stream) {
+    if (!ctx) return GH_EINVAL;
+    if (!(algos & 7) || (algos & ~7)) return fail(ctx, GH_EINVAL, "bad algos mask");
+    if (n_msgs == 0) return GH_OK;
+    if (!d_data || !d_state) return fail(ctx, GH_EINVAL, "d_data / d_state is NULL");
+    if (prior_bytes & 63) return fail(ctx, GH_EINVAL, "prior_bytes must be a multiple of 64");
+    if ((chunk_len & 63) && prior_bytes + chunk_len < msg_len)
+        return fail(ctx, GH_EINVAL, "chunk_len must be a multiple of 64 unless every message ends in this call");
+    if (last_msg_len > msg_len) return fail(ctx, GH_EINVAL, "last_msg_len > msg_len");
+    GhJob j{};
+    j.data = static_cast<const uint8_t*>(d_data);
+    j.stride = stride;
+    j.chunk_len = chunk_len;
+    j.prior = prior_bytes;
+    j.n_msgs = n_msgs;
+    j.msg_len = msg_len;
+    j.last_msg_len = last_msg_len;
+    j.state = d_state;
+    j.sha1 = d_sha1;
+    j.md5 = d_md5;
+    j.sha256 = d_sha256;
+    return device_call(ctx, dev_index, algos, j, cuda_stream);
+}
+
+int gh_generate_device(gh_ctx* ctx, int dev_index, void* d_out, uint64_t seed, uint64_t offset, uint64_t len,
+                       void* cuda_stream) {
+    Device* d = get_dev(ctx, dev_index);
+    if (!d) return fail(ctx, GH_EINVAL, "bad device index");
+    if (len && !d_out) return fail(ctx, GH_EINVAL, "d_out is NULL");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    GH_CUDA(ctx, cudaSetDevice(d->ordinal));
+    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : d->stream;
+    GH_CUDA(ctx, gh_launch_generate(static_cast<uint8_t*>(d_out), seed, offset, len, st));
+    if (!cuda_stream) GH_CUDA(ctx, cudaStreamSynchronize(st));
+    return GH_OK;
+}
+
+// ---- memory helpers ------------------------------------------------------------------------
+int gh_host_alloc(void** out, size_t bytes) {
+    if (!out) return GH_EINVAL;
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? GH_ENOMEM : GH_ECUDA; }
+    return GH_OK;
+}
+int gh_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? GH_OK : GH_ECUDA; }
+int gh_host_register(void* p, size_t bytes) {
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? GH_ENOMEM : GH_ECUDA; }
+    return GH_OK;
+}
+int gh_host_unregister(void* p) { return cudaHostUnregister(p) == cudaSuccess ? GH_OK : GH_ECUDA; }
+
+int gh_device_alloc(gh_ctx* ctx, int dev_index, void** out, size_t bytes) {
+    Device* d = get_dev(ctx, dev_index);
+    if (!d || !out) return GH_EINVAL;
+    GH_CUDA(ctx, cudaSetDevice(d->ordinal));
+    GH_CUDA(ctx, cudaMalloc(out, bytes ? bytes : 1));
+    return GH_OK;
+}
+int gh_device_free(gh_ctx* ctx, int dev_index, void* p) {
+    Device* d = get_dev(ctx, dev_index);
+    if (!d) return GH_EINVAL;
+    GH_CUDA(ctx, cudaSetDevice(d->ordinal));
+    GH_CUDA(ctx, cudaFree(p));
+    return GH_OK;
+}
+int gh_memcpy_d2h(gh_ctx* ctx, int dev_index, void* dst_host, const void* src_dev, size_t bytes) {
+    Device* d = get_dev(ctx, dev_index);
+    if (!d) return GH_EINVAL;
+    GH_CUDA(ctx, cudaSetDevice(d->ordinal));
+    GH_CUDA(ctx, cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+    return GH_OK;
+}
+int gh_memcpy_h2d(gh_ctx* ctx, int dev_index, void* dst_dev, const void* src_host, size_t bytes) {
+    Device* d = get_dev(ctx, dev_index);
+    if (!d) return GH_EINVAL;
+    GH_CUDA(ctx, cudaSetDevice(d->ordinal));
+    GH_CUDA(ctx, cudaMemcpy(dst_dev, src_host, bytes, cudaMemcpyHostToDevice));
+    return GH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,277 @@
+"""gpuhash -- host-side mirror (ctypes) of the Go package `gpuhash` over libgpuhash.so.
+
+The reference is Go, but no Go toolchain exists in this image, so the host
+side that tests and benchmarks drive is this module; go/gpuhash/gpuhash.go is the same surface in
+cgo for a maintainer to build. Names follow the Go package: VerifyPieces / HashParts / S3ETag.
+
+What it replaces in the reference (which has no hashing interface of its own):
+  VerifyPieces -> anacrolix/torrent Torrent.hashPiece + pieceHashed, reached from
+                  internal/downloader/torrent/torrent.go:79-106 (storage seam :41)
+  HashParts    -> minio-go hashMaterials (crypto/md5 + sha256-simd), reached from
+                  internal/uploader/uploader.go:89
+
+There is NO CPU fallback here: importing works anywhere (so the ABI can be inspected), but
+Context() raises GpuHashError unless libgpuhash.so is built and a CUDA device is present.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+SHA1, MD5, SHA256 = 1, 2, 4
+DIGEST_LEN = {SHA1: 20, MD5: 16, SHA256: 32}
+
+GH_OK, GH_EINVAL, GH_ENODEVICE, GH_ENOMEM, GH_ECUDA, GH_ECTX_LOST, GH_ERANGE = range(7)
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG, "libgpuhash.so")
+
+
+class GpuHashError(RuntimeError):
+    def __init__(self, status, what, detail=""):
+        self.status = status
+        super().__init__("%s: status %d (%s)%s" % (what, status, _strerror(status), (": " + detail) if detail else ""))
+
+
+class Span(ctypes.Structure):
+    _fields_ = [("host_ptr", ctypes.c_void_p), ("len", ctypes.c_uint64)]
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("n_devices", ctypes.c_int), ("devices", ctypes.POINTER(ctypes.c_int)),
+                ("slot_bytes", ctypes.c_uint64), ("slots", ctypes.c_int), ("stage_threads", ctypes.c_int)]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("kernel_launches", ctypes.c_uint64), ("h2d_bytes", ctypes.c_uint64),
+                ("d2h_bytes", ctypes.c_uint64), ("kernel_ms", ctypes.c_double), ("wall_ms", ctypes.c_double)]
+
+
+_lib = None
+
+# name -> (restype, argtypes); every symbol include/gpuhash.h declares
+_VP, _U64, _INT, _SZ = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_size_t
+ABI = {
+    "gh_create": (_INT, [ctypes.POINTER(_VP), ctypes.POINTER(Config)]),
+    "gh_destroy": (None, [_VP]),
+    "gh_strerror": (ctypes.c_char_p, [_INT]),
+    "gh_last_error": (ctypes.c_char_p, [_VP]),
+    "gh_device_count": (_INT, [_VP]),
+    "gh_get_stats": (_INT, [_VP, ctypes.POINTER(Stats)]),
+    "gh_version": (ctypes.c_char_p, []),
+    "gh_verify_pieces": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
+    "gh_hash_parts": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _INT, _VP, _VP, _VP]),
+    "gh_s3_etag": (_INT, [_VP, _VP, _U64, ctypes.c_char_p, _SZ]),
+    "gh_verify_pieces_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _VP, _VP, _VP, _VP]),
+    "gh_hash_parts_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _INT, _VP, _VP, _VP, _VP]),
+    "gh_hash_update_device": (_INT, [_VP, _INT, _INT, _VP, _U64, _U64, _U64, _U64, _U64, _U64, _VP, _VP, _VP, _VP, _VP]),
+    "gh_generate_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _U64, _VP]),
+    "gh_host_alloc": (_INT, [ctypes.POINTER(_VP), _SZ]),
+    "gh_host_free": (_INT, [_VP]),
+    "gh_host_register": (_INT, [_VP, _SZ]),
+    "gh_host_unregister": (_INT, [_VP]),
+    "gh_device_alloc": (_INT, [_VP, _INT, ctypes.POINTER(_VP), _SZ]),
+    "gh_device_free": (_INT, [_VP, _INT, _VP]),
+    "gh_memcpy_d2h": (_INT, [_VP, _INT, _VP, _VP, _SZ]),
+    "gh_memcpy_h2d": (_INT, [_VP, _INT, _VP, _VP, _SZ]),
+    "gh_shard_range": (None, [_U64, _INT, _INT, ctypes.POINTER(_U64), ctypes.POINTER(_U64)]),
+}
+
+
+def load():
+    """dlopen libgpuhash.so and type every exported entry point. No device is touched."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GpuHashError(GH_ENODEVICE, "libgpuhash.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`)")
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in ABI.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _strerror(status):
+    try:
+        return load().gh_strerror(status).decode()
+    except Exception:  # library missing: still produce a readable message
+        return "?"
+
+
+def shard_range(n_msgs, n_shards, shard):
+    b, e = ctypes.c_uint64(), ctypes.c_uint64()
+    load().gh_shard_range(n_msgs, n_shards, shard, ctypes.byref(b), ctypes.byref(e))
+    return int(b.value), int(e.value)
+
+
+def count(total, msg_len):
+    return 0 if total == 0 else (total + msg_len - 1) // msg_len
+
+
+def _u8(a):
+    if isinstance(a, np.ndarray):
+        if a.dtype != np.uint8 or not a.flags["C_CONTIGUOUS"]:
+            a = np.ascontiguousarray(a).view(np.uint8).reshape(-1)
+        return a
+    return np.frombuffer(bytes(a), dtype=np.uint8)
+
+
+def _ptr(a):
+    return ctypes.c_void_p(a.ctypes.data) if a is not None and a.size else None
+
+
+class PinnedBuffer:
+    """Page-locked host memory from gh_host_alloc, viewable as a numpy uint8 array."""
+
+    def __init__(self, nbytes):
+        p = ctypes.c_void_p()
+        rc = load().gh_host_alloc(ctypes.byref(p), nbytes)
+        if rc:
+            raise GpuHashError(rc, "gh_host_alloc(%d)" % nbytes)
+        self.ptr, self.nbytes = p.value, nbytes
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * max(nbytes, 1)).from_address(self.ptr))[:nbytes]
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            load().gh_host_free(ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+
+class Context:
+    """One gh_ctx. `devices` is a list of CUDA ordinals (None = all visible)."""
+
+    def __init__(self, devices=None, slot_bytes=0, slots=0, stage_threads=0):
+        L = load()
+        cfg = Config()
+        self._dev_arr = None
+        if devices is not None:
+            self._dev_arr = (ctypes.c_int * len(devices))(*devices)
+            cfg.n_devices = len(devices)
+            cfg.devices = ctypes.cast(self._dev_arr, ctypes.POINTER(ctypes.c_int))
+        cfg.slot_bytes, cfg.slots, cfg.stage_threads = slot_bytes, slots, stage_threads
+        h = ctypes.c_void_p()
+        rc = L.gh_create(ctypes.byref(h), ctypes.byref(cfg))
+        if rc:
+            raise GpuHashError(rc, "gh_create")
+        self.h = h
+        self.L = L
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gh_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def _check(self, rc, what):
+        if rc:
+            raise GpuHashError(rc, what, self.L.gh_last_error(self.h).decode())
+
+    @property
+    def n_devices(self):
+        return self.L.gh_device_count(self.h)
+
+    def stats(self):
+        s = Stats()
+        self._check(self.L.gh_get_stats(self.h, ctypes.byref(s)), "gh_get_stats")
+        return s
+
+    # ---- host-buffer API (names as in the Go package) ------------------------------------
+    @staticmethod
+    def _spans(files):
+        arrs = [_u8(f) for f in files]
+        sp = (Span * max(len(arrs), 1))()
+        total = 0
+        for i, a in enumerate(arrs):
+            sp[i].host_ptr = a.ctypes.data if a.size else None
+            sp[i].len = a.size
+            total += a.size
+        return arrs, sp, total
+
+    def VerifyPieces(self, files, piece_len, expected=None, want_digests=True):
+        """files: list of byte buffers (the torrent's files in info order). Returns
+        (bitmap uint64[], digests uint8[n,20] or None, n_bad)."""
+        arrs, sp, total = self._spans(files)
+        if piece_len <= 0:
+            self._check(self.L.gh_verify_pieces(self.h, sp, len(arrs), 0, None, None, None, None), "gh_verify_pieces")
+        n = count(total, piece_len)
+        exp = _u8(expected) if expected is not None else None
+        if exp is not None and exp.size != 20 * n:
+            raise GpuHashError(GH_EINVAL, "VerifyPieces: expected must hold 20*n_pieces bytes")
+        dig = np.zeros((n, 20), dtype=np.uint8) if want_digests else None
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        nbad = ctypes.c_uint64()
+        rc = self.L.gh_verify_pieces(self.h, sp, len(arrs), piece_len, _ptr(exp), _ptr(dig), _ptr(bitmap),
+                                     ctypes.byref(nbad))
+        self._check(rc, "gh_verify_pieces")
+        return bitmap, dig, int(nbad.value)
+
+    def HashParts(self, files, part_len, algos):
+        """Returns {algo: uint8[n, digest_len]} for each algorithm bit set in `algos`."""
+        arrs, sp, total = self._spans(files)
+        n = count(total, part_len) if part_len > 0 else 0
+        outs = {a: np.zeros((n, DIGEST_LEN[a]), dtype=np.uint8) for a in (SHA1, MD5, SHA256) if algos & a}
+        rc = self.L.gh_hash_parts(self.h, sp, len(arrs), part_len, algos, _ptr(outs.get(SHA1)), _ptr(outs.get(MD5)),
+                                  _ptr(outs.get(SHA256)))
+        self._check(rc, "gh_hash_parts")
+        return outs
+
+    def S3ETag(self, part_md5s):
+        a = _u8(part_md5s)
+        buf = ctypes.create_string_buffer(64)
+        self._check(self.L.gh_s3_etag(self.h, _ptr(a), a.size // 16, buf, 64), "gh_s3_etag")
+        return buf.value.decode()
+
+    # ---- device-resident API (raw device addresses as ints) --------------------------------
+    def device_alloc(self, nbytes, dev=0):
+        p = ctypes.c_void_p()
+        self._check(self.L.gh_device_alloc(self.h, dev, ctypes.byref(p), nbytes), "gh_device_alloc")
+        return p.value
+
+    def device_free(self, ptr, dev=0):
+        self._check(self.L.gh_device_free(self.h, dev, ctypes.c_void_p(ptr)), "gh_device_free")
+
+    def d2h(self, ptr, nbytes, dev=0):
+        out = np.empty(nbytes, dtype=np.uint8)
+        if nbytes:
+            self._check(self.L.gh_memcpy_d2h(self.h, dev, _ptr(out), ctypes.c_void_p(ptr), nbytes), "gh_memcpy_d2h")
+        return out
+
+    def h2d(self, ptr, data, dev=0):
+        a = _u8(data)
+        if a.size:
+            self._check(self.L.gh_memcpy_h2d(self.h, dev, ctypes.c_void_p(ptr), _ptr(a), a.size), "gh_memcpy_h2d")
+
+    def generate(self, d_out, seed, offset, length, dev=0, stream=None):
+        self._check(self.L.gh_generate_device(self.h, dev, ctypes.c_void_p(d_out), seed, offset, length,
+                                              ctypes.c_void_p(stream) if stream else None), "gh_generate_device")
+
+    def verify_pieces_device(self, d_data, total, piece_len, d_expected=None, d_digests=None, d_ok=None, dev=0,
+                             stream=None):
+        vp = ctypes.c_void_p
+        self._check(self.L.gh_verify_pieces_device(self.h, dev, vp(d_data), total, piece_len,
+                                                   vp(d_expected) if d_expected else None,
+                                                   vp(d_digests) if d_digests else None,
+                                                   vp(d_ok) if d_ok else None,
+                                                   vp(stream) if stream else None), "gh_verify_pieces_device")
+
+    def hash_parts_device(self, d_data, total, part_len, algos, d_sha1=None, d_md5=None, d_sha256=None, dev=0,
+                          stream=None):
+        vp = ctypes.c_void_p
+        self._check(self.L.gh_hash_parts_device(self.h, dev, vp(d_data), total, part_len, algos,
+                                                vp(d_sha1) if d_sha1 else None, vp(d_md5) if d_md5 else None,
+                                                vp(d_sha256) if d_sha256 else None,
+                                                vp(stream) if stream else None), "gh_hash_parts_device")
+
+    def hash_update_device(self, algos, d_data, stride, chunk_len, prior, n_msgs, msg_len, last_msg_len, d_state,
+                           d_sha1=None, d_md5=None, d_sha256=None, dev=0, stream=None):
+        vp = ctypes.c_void_p
+        self._check(self.L.gh_hash_update_device(self.h, dev, algos, vp(d_data), stride, chunk_len, prior, n_msgs,
+                                                 msg_len, last_msg_len, vp(d_state),
+                                                 vp(d_sha1) if d_sha1 else None, vp(d_md5) if d_md5 else None,
+                                                 vp(d_sha256) if d_sha256 else None,
+                                                 vp(stream) if stream else None), "gh_hash_update_device")

@@ -1,0 +1,160 @@
+/*
+ * gpuhash.h -- C ABI of libgpuhash.so, the B200 (sm_100a) batched content hasher.
+ *
+ * This is the drop-in boundary for the one data-parallel path of tritonmedia/downloader-go:
+ *   - SHA-1 verification of torrent pieces, executed by anacrolix/torrent v1.15.2 (go.mod:6) between
+ *     reference internal/downloader/torrent/torrent.go:79 (t.DownloadAll) and :106 (client.WaitAll);
+ *     the storage seam is torrent.go:41 (clientConfig.DefaultStorage = storage.NewFile(baseDir)).
+ *   - per-part MD5 (ETag / Content-MD5) and SHA-256 (SigV4 payload hash), executed by
+ *     minio-go/v6 v6.0.55 (go.mod:11) under reference internal/uploader/uploader.go:89
+ *     (s3client.PutObjectWithContext).
+ * The reference defines no hashing interface of its own, so each entry point
+ * below names the third-party call it replaces and the reference line that reaches it.
+ *
+ * Conventions
+ *   - every function returns an int status, GH_OK == 0; gh_strerror() maps it to a static string.
+ *   - plain pointers and sizes only; no C++/torch types; no exceptions cross the boundary.
+ *   - the caller owns every buffer it passes; one-shot calls are synchronous and never retain a
+ *     caller pointer after returning (the cgo pointer rule). Long-lived memory (staging ring,
+ *     midstates) is allocated by the library.
+ *   - a gh_ctx may be used from several OS threads; calls are serialised per context. The library
+ *     calls cudaSetDevice itself on entry (goroutines migrate between OS threads).
+ *   - there is NO CPU fallback: without a usable CUDA device gh_create fails with GH_ENODEVICE.
+ *   - digests are raw bytes in the standard byte order (what Go's hash.Hash.Sum returns).
+ *   - bitmaps: bit (i & 63) of word (i >> 6) is 1 iff piece i matched its expected SHA-1.
+ */
+#ifndef GPUHASH_H
+#define GPUHASH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gh_ctx gh_ctx;
+
+enum {
+    GH_OK = 0,
+    GH_EINVAL = 1,     /* bad argument (NULL where data is required, zero piece length, ...) */
+    GH_ENODEVICE = 2,  /* no CUDA device / driver, or requested ordinal absent */
+    GH_ENOMEM = 3,     /* host or device allocation failed */
+    GH_ECUDA = 4,      /* a CUDA call failed; gh_last_error(ctx) has the text */
+    GH_ECTX_LOST = 5,  /* sticky device error: destroy the context */
+    GH_ERANGE = 6      /* size beyond a documented limit */
+};
+
+enum { GH_SHA1 = 1, GH_MD5 = 2, GH_SHA256 = 4 }; /* algos bitmask; GH_MD5|GH_SHA256 = one fused pass */
+
+typedef struct {
+    int        n_devices;     /* 0 = every visible device */
+    const int* devices;       /* CUDA ordinals, NULL = 0..n_devices-1 */
+    uint64_t   slot_bytes;    /* device bytes per ring slot, 0 = default (256 MiB) */
+    int        slots;         /* ring slots per device, 0 = default (3), minimum 2 */
+    int        stage_threads; /* host threads copying pageable spans into the pinned ring, 0 = default (4) */
+} gh_config;
+
+/* A run of stream bytes in host memory. The logical stream is the concatenation of the spans, in
+ * order: exactly BEP 3's "files concatenated in info order" (what anacrolix/torrent/storage ReadAt
+ * presents to Torrent.hashPiece), or one file for the uploader (uploader.go:73-89). */
+typedef struct {
+    const void* host_ptr;
+    uint64_t    len;
+} gh_span;
+
+typedef struct {
+    uint64_t kernel_launches;  /* hashing kernels launched by this context so far */
+    uint64_t h2d_bytes;        /* payload bytes copied host -> device */
+    uint64_t d2h_bytes;        /* result bytes copied device -> host */
+    double   kernel_ms;        /* CUDA-event time of the hashing kernels of the LAST call, summed */
+    double   wall_ms;          /* host wall time of the LAST call */
+} gh_stats;
+
+/* ---- lifecycle ---------------------------------------------------------------------------- */
+int         gh_create(gh_ctx** out, const gh_config* cfg /* NULL = defaults */);
+void        gh_destroy(gh_ctx* ctx);
+const char* gh_strerror(int status);
+const char* gh_last_error(gh_ctx* ctx);           /* detail of the last failure on this context */
+int         gh_device_count(gh_ctx* ctx);
+int         gh_get_stats(gh_ctx* ctx, gh_stats* out);
+const char* gh_version(void);
+
+/* ---- host-buffer (end-to-end) entry points -------------------------------------------------- */
+
+/* Batched piece verification. Replaces, for a whole batch of pieces at once, anacrolix/torrent
+ * Torrent.hashPiece + pieceHashed (crypto/sha1 over piece.Storage(), compare with
+ * info.Pieces[20i:20i+20]) that run under reference torrent.go:79-106.
+ * piece i = stream[i*piece_len, min((i+1)*piece_len, total)), only the last piece may be short.
+ * expected: 20*n_pieces bytes or NULL (then only digests are produced and every bit is 0).
+ * digests_out: 20*n_pieces bytes or NULL. ok_bitmap_out: ceil(n_pieces/64) words or NULL.
+ * n_bad_out: number of pieces whose digest differs from expected, or NULL.
+ * Pieces are sharded over the context's devices in contiguous, 64-piece-aligned ranges. */
+int gh_verify_pieces(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t piece_len,
+                     const uint8_t* expected, uint8_t* digests_out, uint64_t* ok_bitmap_out,
+                     uint64_t* n_bad_out);
+
+/* Batched per-part hashing. Replaces minio-go hashMaterials (crypto/md5 + sha256-simd over one
+ * buffered part) that runs under reference uploader.go:89; the sums are what
+ * minio.Core.PutObjectPart(..., md5Base64, sha256Hex, ...) accepts precomputed.
+ * part k = stream[k*part_len, min((k+1)*part_len, total)). algos is a GH_* bitmask; outputs for
+ * unselected algorithms may be NULL. sha1_out 20*n, md5_out 16*n, sha256_out 32*n bytes. */
+int gh_hash_parts(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t part_len, int algos,
+                  uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out);
+
+/* S3 multipart ETag of n binary part MD5s: hex(md5(concat)) + "-" + n (what the server returns for
+ * the upload started at uploader.go:89; computed on the device like any other message).
+ * out needs at least 56 bytes. */
+int gh_s3_etag(gh_ctx* ctx, const uint8_t* part_md5s, uint64_t n_parts, char* out, size_t out_len);
+
+/* ---- device-resident entry points (payload already in HBM; "kernel-only" numbers) ------------ */
+
+/* Same contract as gh_verify_pieces / gh_hash_parts but every pointer is a DEVICE pointer on
+ * device `dev_index` (index into the context's device list). d_ok_words: ceil(n/32) uint32 words
+ * (the uint64 host bitmap viewed as little-endian uint32 pairs). cuda_stream: a cudaStream_t cast to
+ * void*; the launch is asynchronous on it. NULL = the context's own stream and the call returns
+ * after the kernel has finished. d_data should be 16-byte aligned and msg_len a multiple of 16 for
+ * the staged (coalesced) path; anything else takes the byte-granular path. */
+int gh_verify_pieces_device(gh_ctx* ctx, int dev_index, const void* d_data, uint64_t total,
+                            uint64_t piece_len, const uint8_t* d_expected, uint8_t* d_digests,
+                            uint32_t* d_ok_words, void* cuda_stream);
+int gh_hash_parts_device(gh_ctx* ctx, int dev_index, const void* d_data, uint64_t total,
+                         uint64_t part_len, int algos, uint8_t* d_sha1, uint8_t* d_md5,
+                         uint8_t* d_sha256, void* cuda_stream);
+
+/* Resumable form for messages longer than a staging slot (midstates stay on the device).
+ * Absorbs chunk_len bytes of each of n_msgs messages: message m's bytes for this call start at
+ * d_data + m*stride. prior_bytes (a multiple of 64) is what earlier calls absorbed of every message;
+ * msg_len / last_msg_len are the full message lengths. A message whose end falls inside this call is
+ * padded and its digest written; d_state (n_msgs * 12 uint32, library layout) carries the midstates
+ * between calls and must be the same buffer throughout. chunk_len must be a multiple of 64 unless
+ * every message ends in this call. */
+int gh_hash_update_device(gh_ctx* ctx, int dev_index, int algos, const void* d_data, uint64_t stride,
+                          uint64_t chunk_len, uint64_t prior_bytes, uint64_t n_msgs, uint64_t msg_len,
+                          uint64_t last_msg_len, uint32_t* d_state, uint8_t* d_sha1, uint8_t* d_md5,
+                          uint8_t* d_sha256, void* cuda_stream);
+
+/* Synthetic stream of SURVEY.md Appendix C, generated on the device: byte k of stream(seed) for
+ * k in [offset, offset+len) written to d_out. (Test / benchmark input; no reference counterpart.) */
+int gh_generate_device(gh_ctx* ctx, int dev_index, void* d_out, uint64_t seed, uint64_t offset,
+                       uint64_t len, void* cuda_stream);
+
+/* ---- memory helpers ------------------------------------------------------------------------- */
+/* Pinned host memory lets spans go host->device by DMA without the staging copy. */
+int gh_host_alloc(void** out, size_t bytes);
+int gh_host_free(void* p);
+int gh_host_register(void* p, size_t bytes);
+int gh_host_unregister(void* p);
+int gh_device_alloc(gh_ctx* ctx, int dev_index, void** out, size_t bytes);
+int gh_device_free(gh_ctx* ctx, int dev_index, void* p);
+int gh_memcpy_d2h(gh_ctx* ctx, int dev_index, void* dst_host, const void* src_dev, size_t bytes);
+int gh_memcpy_h2d(gh_ctx* ctx, int dev_index, void* dst_dev, const void* src_host, size_t bytes);
+
+/* Contiguous 64-aligned range of messages that shard `shard` of `n_shards` owns:
+ * [*begin, *end). Used for the in-context multi-GPU split and by one-process-per-GPU callers. */
+void gh_shard_range(uint64_t n_msgs, int n_shards, int shard, uint64_t* begin, uint64_t* end);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUHASH_H */
