@@ -3,7 +3,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define GH_STATE_WORDS 12 /* per message: SHA-1 uses 0..4, MD5 0..3, SHA-256 4..11 (MD5|SHA-256 share a row) */
+#ifndef GH_STATE_WORDS
+#define GH_STATE_WORDS 17
+#endif
+/* rows per message: MD5 0..3, SHA-256 4..11, SHA-1 12..16 (disjoint: any mix of algorithms may share a batch) */
 
 // One launch of the lane-per-message hasher. Message m's bytes for this launch start at
 // data + m*stride; `prior` bytes of every message were absorbed by earlier launches.

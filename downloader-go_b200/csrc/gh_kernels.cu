@@ -90,7 +90,7 @@ struct Lane {
     __device__ __forceinline__ void load(const uint32_t* st, uint64_t n, uint64_t m) {
         if constexpr (ALGOS & GH_SHA1) {
 #pragma unroll
-            for (int i = 0; i < 5; i++) s1[i] = st[i * n + m];
+            for (int i = 0; i < 5; i++) s1[i] = st[(12 + i) * n + m];
         }
         if constexpr (ALGOS & GH_MD5) {
 #pragma unroll
@@ -104,7 +104,7 @@ struct Lane {
     __device__ __forceinline__ void store(uint32_t* st, uint64_t n, uint64_t m) const {
         if constexpr (ALGOS & GH_SHA1) {
 #pragma unroll
-            for (int i = 0; i < 5; i++) st[i * n + m] = s1[i];
+            for (int i = 0; i < 5; i++) st[(12 + i) * n + m] = s1[i];
         }
         if constexpr (ALGOS & GH_MD5) {
 #pragma unroll

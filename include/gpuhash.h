@@ -47,6 +47,8 @@ enum {
 
 enum { GH_SHA1 = 1, GH_MD5 = 2, GH_SHA256 = 4 }; /* algos bitmask; GH_MD5|GH_SHA256 = one fused pass */
 
+#define GH_STATE_WORDS 17 /* uint32 midstate words per message in a d_state buffer (all three algorithms) */
+
 typedef struct {
     int        n_devices;     /* 0 = every visible device */
     const int* devices;       /* CUDA ordinals, NULL = 0..n_devices-1 */
@@ -126,7 +128,7 @@ int gh_hash_parts_device(gh_ctx* ctx, int dev_index, const void* d_data, uint64_
  * Absorbs chunk_len bytes of each of n_msgs messages: message m's bytes for this call start at
  * d_data + m*stride. prior_bytes (a multiple of 64) is what earlier calls absorbed of every message;
  * msg_len / last_msg_len are the full message lengths. A message whose end falls inside this call is
- * padded and its digest written; d_state (n_msgs * 12 uint32, library layout) carries the midstates
+ * padded and its digest written; d_state (n_msgs * GH_STATE_WORDS uint32, library layout) carries the midstates
  * between calls and must be the same buffer throughout. chunk_len must be a multiple of 64 unless
  * every message ends in this call. */
 int gh_hash_update_device(gh_ctx* ctx, int dev_index, int algos, const void* d_data, uint64_t stride,

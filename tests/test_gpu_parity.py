@@ -149,7 +149,7 @@ def test_pinned_spans_direct_dma(gh):
 
 
 @pytest.mark.parametrize("pinned", [False, True])
-@pytest.mark.parametrize("algos", [gpuhash.SHA1, gpuhash.MD5 | gpuhash.SHA256])
+@pytest.mark.parametrize("algos", [gpuhash.SHA1, gpuhash.MD5 | gpuhash.SHA256, gpuhash.SHA1 | gpuhash.MD5 | gpuhash.SHA256])
 def test_chunk_interleaved_ring(algos, pinned):
     """Messages larger than the ring window: the host ring streams one sub-chunk of every message
     per window and the kernel carries midstates between launches (config 3's regime)."""
@@ -282,7 +282,8 @@ def test_device_parts_cfg3_reduced_and_golden(gh, golden):
     assert np.array_equal(s, oracle.hash_msgs(oracle.SHA256, host, P, 6))
 
 
-@pytest.mark.parametrize("algos", [gpuhash.SHA1, gpuhash.MD5, gpuhash.SHA256, gpuhash.MD5 | gpuhash.SHA256])
+@pytest.mark.parametrize("algos", [gpuhash.SHA1, gpuhash.MD5, gpuhash.SHA256, gpuhash.MD5 | gpuhash.SHA256,
+                                   gpuhash.SHA1 | gpuhash.MD5 | gpuhash.SHA256])
 def test_resumable_update_device(gh, algos):
     """init/update/final with midstates on the device: three unequal windows, short last message."""
     torch = _torch()
@@ -290,7 +291,7 @@ def test_resumable_update_device(gh, algos):
     total = (n - 1) * L + last
     host = oracle.gen(11, 0, total)
     d = torch.from_numpy(host).cuda()
-    state = torch.zeros(n * 12, dtype=torch.int32, device="cuda")
+    state = torch.zeros(n * 17, dtype=torch.int32, device="cuda")
     outs = {a: torch.zeros(n * gpuhash.DIGEST_LEN[a], dtype=torch.uint8, device="cuda") for a, _ in ALGS}
     prior = 0
     for chunk in (4096, 8192, 2 * 4096 + 128):
