@@ -502,3 +502,81 @@ cudaError_t gh_launch_generate(uint8_t* d_out, uint64_t seed, uint64_t offset, u
     gh_generate<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(d_out, seed, offset, len);
     return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------- fixed-scratch entry point
+// gh_hash_update_device_noalloc (include/gpuhash.h): the resumable hasher with its midstates in a
+// statically allocated device array instead of a caller- or library-allocated buffer. The array is
+// part of the library image: every GPU that loads libgpuhash.so holds these
+// GH_NOALLOC_MAX_MSGS * GH_STATE_WORDS * 4 bytes (1 088 KiB) until the process exits.
+#include <mutex>
+
+static __device__ __align__(256) uint32_t g_noalloc_state[GH_NOALLOC_MAX_MSGS * GH_STATE_WORDS];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_ptr[kNoallocMaxDevices];  // device address of g_noalloc_state per CUDA ordinal; null = not set up
+int g_noalloc_sms[kNoallocMaxDevices];
+}  // namespace
+
+extern "C" int gh_hash_update_device_noalloc(int cuda_device, int algos, const void* d_data, uint64_t stride,
+                                             uint64_t chunk_len, uint64_t prior_bytes, uint64_t n_msgs,
+                                             uint64_t msg_len, uint64_t last_msg_len, uint8_t* d_sha1,
+                                             uint8_t* d_md5, uint8_t* d_sha256, void* cuda_stream) {
+    if (cuda_device < 0 || cuda_device >= kNoallocMaxDevices) return GH_ENODEVICE;
+    if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256))) return GH_EINVAL;
+    if (n_msgs == 0) return GH_OK;
+    if (n_msgs > GH_NOALLOC_MAX_MSGS) return GH_ERANGE;  // the static array holds no more midstates than that
+    if (!d_data) return GH_EINVAL;
+    if (prior_bytes & 63) return GH_EINVAL;
+    if ((chunk_len & 63) && prior_bytes + chunk_len < msg_len) return GH_EINVAL;
+    if (last_msg_len > msg_len) return GH_EINVAL;
+    if (cudaSetDevice(cuda_device) != cudaSuccess) {
+        cudaGetLastError();
+        return GH_ENODEVICE;
+    }
+    uint32_t* state = nullptr;
+    int sms = 0;
+    {
+        // Once per device, with that device current: the array's name is only a host-side handle, the
+        // kernel needs the address the symbol has on THIS device.
+        std::lock_guard<std::mutex> g(g_noalloc_mu);
+        if (!g_noalloc_ptr[cuda_device]) {
+            if (gh_kernels_init_device() != cudaSuccess) return GH_ECUDA;
+            void* p = nullptr;
+            if (cudaGetSymbolAddress(&p, g_noalloc_state) != cudaSuccess || !p) {
+                cudaGetLastError();
+                return GH_ECUDA;
+            }
+            int n = 0;
+            if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, cuda_device) != cudaSuccess) return GH_ECUDA;
+            g_noalloc_sms[cuda_device] = n;
+            g_noalloc_ptr[cuda_device] = static_cast<uint32_t*>(p);
+        }
+        state = g_noalloc_ptr[cuda_device];
+        sms = g_noalloc_sms[cuda_device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);  // null = the device's default stream
+    if (prior_bytes == 0) {
+        // A new batch starts: drop whatever the previous batch left in the part of the array this one uses.
+        if (cudaMemsetAsync(state, 0, n_msgs * GH_STATE_WORDS * sizeof(uint32_t), st) != cudaSuccess) return GH_ECUDA;
+    }
+    GhJob j{};
+    j.data = static_cast<const uint8_t*>(d_data);
+    j.stride = stride;
+    j.chunk_len = chunk_len;
+    j.prior = prior_bytes;
+    j.n_msgs = n_msgs;
+    j.msg_len = msg_len;
+    j.last_msg_len = last_msg_len;
+    j.state = state;
+    j.sha1 = d_sha1;
+    j.md5 = d_md5;
+    j.sha256 = d_sha256;
+    if (algos & GH_SHA1)
+        if (gh_launch_hash(GH_SHA1, j, sms, st) != cudaSuccess) return GH_ECUDA;
+    if (algos & (GH_MD5 | GH_SHA256))
+        if (gh_launch_hash(algos & (GH_MD5 | GH_SHA256), j, sms, st) != cudaSuccess) return GH_ECUDA;
+    if (!cuda_stream && cudaStreamSynchronize(st) != cudaSuccess) return GH_ECUDA;
+    return GH_OK;
+}

@@ -65,6 +65,7 @@ ABI = {
     "gh_verify_pieces_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _VP, _VP, _VP, _VP]),
     "gh_hash_parts_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _INT, _VP, _VP, _VP, _VP]),
     "gh_hash_update_device": (_INT, [_VP, _INT, _INT, _VP, _U64, _U64, _U64, _U64, _U64, _U64, _VP, _VP, _VP, _VP, _VP]),
+    "gh_hash_update_device_noalloc": (_INT, [_INT, _INT, _VP, _U64, _U64, _U64, _U64, _U64, _U64, _VP, _VP, _VP, _VP]),
     "gh_generate_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _U64, _VP]),
     "gh_host_alloc": (_INT, [ctypes.POINTER(_VP), _SZ]),
     "gh_host_free": (_INT, [_VP]),
@@ -98,6 +99,23 @@ def _strerror(status):
         return load().gh_strerror(status).decode()
     except Exception:  # library missing: still produce a readable message
         return "?"
+
+
+NOALLOC_MAX_MSGS = 16384
+
+
+def hash_update_device_noalloc(cuda_device, algos, d_data, stride, chunk_len, prior, n_msgs, msg_len, last_msg_len,
+                               d_sha1=None, d_md5=None, d_sha256=None, stream=None):
+    """gh_hash_update_device_noalloc: the resumable hasher for callers that must not allocate device
+    memory (midstates sit in a fixed array inside the library, at most NOALLOC_MAX_MSGS messages).
+    Needs no Context. Raises GpuHashError(GH_ERANGE) for batches beyond the fixed array."""
+    vp = ctypes.c_void_p
+    rc = load().gh_hash_update_device_noalloc(cuda_device, algos, vp(d_data), stride, chunk_len, prior, n_msgs, msg_len,
+                                              last_msg_len, vp(d_sha1) if d_sha1 else None,
+                                              vp(d_md5) if d_md5 else None, vp(d_sha256) if d_sha256 else None,
+                                              vp(stream) if stream else None)
+    if rc:
+        raise GpuHashError(rc, "gh_hash_update_device_noalloc")
 
 
 def shard_range(n_msgs, n_shards, shard):

@@ -136,6 +136,33 @@ int gh_hash_update_device(gh_ctx* ctx, int dev_index, int algos, const void* d_d
                           uint64_t last_msg_len, uint32_t* d_state, uint8_t* d_sha1, uint8_t* d_md5,
                           uint8_t* d_sha256, void* cuda_stream);
 
+/* gh_hash_update_device for callers that cannot allocate device memory. It has no counterpart in the
+ * reference (which has no device code); it exists because of who calls this library. A download
+ * worker sizes its payload buffers and staging ring to the HBM it has been given, so by the time a
+ * job reaches hashing there may be nothing left for a midstate buffer and a cudaMalloc would fail
+ * after the expensive part (the download) is already done. Other callers run where asking the CUDA
+ * runtime for memory is off the table altogether: inside a host callback, or on a latency-sensitive
+ * thread that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply.
+ *
+ * Same arguments and results as gh_hash_update_device, except: there is no context (cuda_device is
+ * a CUDA ordinal, made current by the call) and no d_state -- the midstates live in a fixed array
+ * inside the library image, GH_NOALLOC_MAX_MSGS * GH_STATE_WORDS * 4 bytes on every GPU that loads
+ * the library, held until the process exits. n_msgs > GH_NOALLOC_MAX_MSGS is refused with GH_ERANGE
+ * before anything is launched. The call makes no cudaMalloc/cudaFree and uses no allocating
+ * routine; inputs and outputs remain the caller's buffers.
+ *
+ * The first call on a device looks up the array's address on that device and sets kernel
+ * attributes; make that first call before opening any stream capture. All calls on a device share
+ * the one array: a batch's first call (prior_bytes == 0) clears the part it will use, later calls of
+ * the batch continue from what the previous call left, and two batches in flight on the same GPU at
+ * once (different streams or threads) overwrite each other's midstates -- run them one after another.
+ * cuda_stream NULL = the device's default stream, and the call returns after the work is done. */
+#define GH_NOALLOC_MAX_MSGS 16384
+int gh_hash_update_device_noalloc(int cuda_device, int algos, const void* d_data, uint64_t stride,
+                                  uint64_t chunk_len, uint64_t prior_bytes, uint64_t n_msgs,
+                                  uint64_t msg_len, uint64_t last_msg_len, uint8_t* d_sha1,
+                                  uint8_t* d_md5, uint8_t* d_sha256, void* cuda_stream);
+
 /* Synthetic stream of SURVEY.md Appendix C, generated on the device: byte k of stream(seed) for
  * k in [offset, offset+len) written to d_out. (Test / benchmark input; no reference counterpart.) */
 int gh_generate_device(gh_ctx* ctx, int dev_index, void* d_out, uint64_t seed, uint64_t offset,
