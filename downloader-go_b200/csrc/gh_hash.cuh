@@ -27,13 +27,29 @@ __device__ __forceinline__ uint32_t f_maj(uint32_t x, uint32_t y, uint32_t z) { 
 __device__ __forceinline__ uint32_t f_xor3(uint32_t x, uint32_t y, uint32_t z) { return lop3<0x96>(x, y, z); } // x^y^z
 __device__ __forceinline__ uint32_t f_md5i(uint32_t x, uint32_t y, uint32_t z) { return lop3<0x39>(x, y, z); } // y^(x|~z)
 
+// Two-input add on the FMA pipe. The integer ALU pipe (LOP3/SHF/IADD3/PRMT, 64 lanes/clk/SM) is what
+// bounds these kernels while the FMA pipe (IMAD, another 64 lanes/clk/SM) idles; x*one+y with `one` a
+// kernel parameter that ptxas cannot fold is an IMAD, so the additions of a round move over there and
+// the ALU pipe keeps only the Boolean functions and rotates. FMA_ADDS=false gives the plain form.
+template <bool FMA_ADDS>
+__device__ __forceinline__ uint32_t addf(uint32_t x, uint32_t y, uint32_t one) {
+    if constexpr (FMA_ADDS) {
+        uint32_t r;
+        asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(one), "r"(y));
+        return r;
+    } else {
+        return x + y;
+    }
+}
+
 // ------------------------------------------------------------------------------------ SHA-1
 __device__ __forceinline__ void sha1_init(uint32_t (&s)[5]) {
     s[0] = 0x67452301u; s[1] = 0xefcdab89u; s[2] = 0x98badcfeu; s[3] = 0x10325476u; s[4] = 0xc3d2e1f0u;
 }
 
 // w: the block as sixteen big-endian-decoded words; used as the schedule ring and clobbered.
-__device__ __forceinline__ void sha1_compress(uint32_t (&s)[5], uint32_t (&w)[16]) {
+template <bool FMA_ADDS = false>
+__device__ __forceinline__ void sha1_compress(uint32_t (&s)[5], uint32_t (&w)[16], uint32_t one = 1) {
     uint32_t a = s[0], b = s[1], c = s[2], d = s[3], e = s[4];
 #pragma unroll
     for (int t = 0; t < 80; t++) {
@@ -49,7 +65,13 @@ __device__ __forceinline__ void sha1_compress(uint32_t (&s)[5], uint32_t (&w)[16
         else if (t < 40) { f = f_xor3(b, c, d); k = 0x6ed9eba1u; }
         else if (t < 60) { f = f_maj(b, c, d);  k = 0x8f1bbcdcu; }
         else             { f = f_xor3(b, c, d); k = 0xca62c1d6u; }
-        uint32_t tmp = rotl(a, 5) + f + (e + k + wt);
+        uint32_t tmp;
+        if constexpr (FMA_ADDS) {
+            // (wt + k) and (+ e) are off the critical path; the last add fuses with rotl5 into LEA.HI
+            tmp = rotl(a, 5) + addf<true>(addf<true>(addf<true>(wt, k, one), e, one), f, one);
+        } else {
+            tmp = rotl(a, 5) + f + (e + k + wt);
+        }
         e = d; d = c; c = rotl(b, 30); b = a; a = tmp;
     }
     s[0] += a; s[1] += b; s[2] += c; s[3] += d; s[4] += e;
@@ -130,7 +152,8 @@ __device__ __forceinline__ uint32_t S256_s0(uint32_t x) { return f_xor3(rotr(x, 
 __device__ __forceinline__ uint32_t S256_s1(uint32_t x) { return f_xor3(rotr(x, 17), rotr(x, 19), x >> 10); }
 
 // w: the block as sixteen big-endian-decoded words; used as the schedule ring and clobbered.
-__device__ __forceinline__ void sha256_compress(uint32_t (&s)[8], uint32_t (&w)[16]) {
+template <bool FMA_ADDS = false>
+__device__ __forceinline__ void sha256_compress(uint32_t (&s)[8], uint32_t (&w)[16], uint32_t one = 1) {
     uint32_t v[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) v[i] = s[i];
@@ -140,17 +163,30 @@ __device__ __forceinline__ void sha256_compress(uint32_t (&s)[8], uint32_t (&w)[
         if (t < 16) {
             wt = w[t];
         } else {
-            wt = S256_s1(w[(t - 2) & 15]) + w[(t - 7) & 15] + S256_s0(w[(t - 15) & 15]) + w[t & 15];
+            if constexpr (FMA_ADDS)
+                wt = addf<true>(addf<true>(S256_s1(w[(t - 2) & 15]), w[(t - 7) & 15], one),
+                                addf<true>(S256_s0(w[(t - 15) & 15]), w[t & 15], one), one);
+            else
+                wt = S256_s1(w[(t - 2) & 15]) + w[(t - 7) & 15] + S256_s0(w[(t - 15) & 15]) + w[t & 15];
             w[t & 15] = wt;
         }
         // working variables a..h are v[(0 - t) & 7] .. v[(7 - t) & 7]: rotate by renaming, not by moves
         uint32_t& a = v[(0 - t) & 7]; uint32_t& b = v[(1 - t) & 7]; uint32_t& c = v[(2 - t) & 7];
         uint32_t& d = v[(3 - t) & 7]; uint32_t& e = v[(4 - t) & 7]; uint32_t& f = v[(5 - t) & 7];
         uint32_t& g = v[(6 - t) & 7]; uint32_t& h = v[(7 - t) & 7];
-        uint32_t t1 = h + S256_S1(e) + f_ch(e, f, g) + (K256[t] + wt);
-        uint32_t t2 = S256_S0(a) + f_maj(a, b, c);
-        d += t1;
-        h = t1 + t2;
+        if constexpr (FMA_ADDS) {
+            // h + K + wt is ready long before e settles; Sigma1/Ch/Sigma0/Maj stay on the ALU pipe
+            const uint32_t hk = addf<true>(addf<true>(wt, K256[t], one), h, one);
+            const uint32_t t1 = addf<true>(addf<true>(hk, f_ch(e, f, g), one), S256_S1(e), one);
+            const uint32_t t2 = addf<true>(S256_S0(a), f_maj(a, b, c), one);
+            d = addf<true>(d, t1, one);
+            h = addf<true>(t1, t2, one);
+        } else {
+            uint32_t t1 = h + S256_S1(e) + f_ch(e, f, g) + (K256[t] + wt);
+            uint32_t t2 = S256_S0(a) + f_maj(a, b, c);
+            d += t1;
+            h = t1 + t2;
+        }
     }
 #pragma unroll
     for (int i = 0; i < 8; i++) s[i] += v[i];

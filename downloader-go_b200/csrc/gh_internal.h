@@ -30,6 +30,7 @@ struct GhJob {
     uint64_t first_msg;
     uint64_t count;
     uint32_t tma_inner;
+    uint32_t one;  // always 1; a kernel parameter so that ptxas keeps x*one+y as an IMAD (gh_hash.cuh addf)
 };
 
 // Launches the hasher for `algos` (GH_SHA1, GH_MD5, GH_SHA256 or GH_MD5|GH_SHA256) on `stream`.

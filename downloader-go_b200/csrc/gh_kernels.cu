@@ -21,6 +21,7 @@
 #include "gh_internal.h"
 
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/gpuhash.h"
@@ -32,12 +33,12 @@ using namespace ghd;
 
 constexpr int kTileRowBytes = 128;                       // inner box extent = the swizzle span
 constexpr int kTileBytes = 32 * kTileRowBytes;           // one TMA box: 32 messages x 128 B
-constexpr int kTilesPerStage = 2;                        // 256 B (4 blocks) of every message per stage
-constexpr int kChunk = kTilesPerStage * kTileRowBytes;
 constexpr int kStages = 2;
-constexpr int kWarpTiles = kStages * kTilesPerStage;
-constexpr int kWarpSmem = kWarpTiles * kTileBytes;       // tiles only; mbarriers live after all tiles
 constexpr int kMaxWarpsPerBlock = 4;
+// TPS = tiles per stage: 2 (256 B = 4 blocks of every message per stage, 16 KiB of shared memory per
+// warp, 13 warps/SM) when there are many warps, 4 (8 blocks per stage, half the barrier traffic) when
+// warps are few and shared memory is not what limits residency.
+__host__ __device__ constexpr int warp_smem(int tps) { return kStages * tps * kTileBytes; }  // tiles only; mbarriers follow all tiles
 
 // ---------------------------------------------------------------------------- mbarrier / TMA PTX
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -48,9 +49,6 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
@@ -75,11 +73,12 @@ __device__ __forceinline__ void tma_load_box(uint32_t dst, const CUtensorMap* tm
 }
 
 // ---------------------------------------------------------------------------- per-lane hash state
-template <int ALGOS>
+template <int ALGOS, bool FMA>
 struct Lane {
     uint32_t s1[5];
     uint32_t m5[4];
     uint32_t s2[8];
+    uint32_t one;  // the kernel parameter 1, multiplier of the IMAD-based adds (gh_hash.cuh addf)
 
     __device__ __forceinline__ void init() {
         if constexpr (ALGOS & GH_SHA1) sha1_init(s1);
@@ -122,13 +121,13 @@ struct Lane {
             uint32_t w[16];
 #pragma unroll
             for (int i = 0; i < 16; i++) w[i] = bswap(r[i]);
-            sha256_compress(s2, w);
+            sha256_compress<FMA>(s2, w, one);
         }
         if constexpr (ALGOS & GH_SHA1) {
             uint32_t w[16];
 #pragma unroll
             for (int i = 0; i < 16; i++) w[i] = bswap(r[i]);
-            sha1_compress(s1, w);
+            sha1_compress<FMA>(s1, w, one);
         }
     }
     // the block that carries the 64-bit message bit length in bytes 56..63 (words 14, 15 of r ignored)
@@ -146,21 +145,21 @@ struct Lane {
 #pragma unroll
             for (int i = 0; i < 14; i++) w[i] = bswap(r[i]);
             w[14] = hi; w[15] = lo;  // FIPS 180-4 5.1.1: big-endian 64-bit length
-            sha256_compress(s2, w);
+            sha256_compress<FMA>(s2, w, one);
         }
         if constexpr (ALGOS & GH_SHA1) {
             uint32_t w[16];
 #pragma unroll
             for (int i = 0; i < 14; i++) w[i] = bswap(r[i]);
             w[14] = hi; w[15] = lo;
-            sha1_compress(s1, w);
+            sha1_compress<FMA>(s1, w, one);
         }
     }
 };
 
 // Padding (FIPS 180-4 5.1.1 / RFC 1321 3.1): tail = the rem (< 64) bytes after the last full block.
-template <int ALGOS>
-__device__ __noinline__ void finalize(Lane<ALGOS>& L, const uint8_t* tail, uint32_t rem, uint64_t total_len) {
+template <int ALGOS, bool FMA>
+__device__ __noinline__ void finalize(Lane<ALGOS, FMA>& L, const uint8_t* tail, uint32_t rem, uint64_t total_len) {
     uint32_t r[16];
 #pragma unroll
     for (int i = 0; i < 16; i++) {
@@ -182,8 +181,8 @@ __device__ __noinline__ void finalize(Lane<ALGOS>& L, const uint8_t* tail, uint3
     L.absorb_with_length(r, bits);
 }
 
-template <int ALGOS>
-__device__ __forceinline__ bool emit(const Lane<ALGOS>& L, const GhJob& job, uint64_t m) {
+template <int ALGOS, bool FMA>
+__device__ __forceinline__ bool emit(const Lane<ALGOS, FMA>& L, const GhJob& job, uint64_t m) {
     bool ok = false;
     if constexpr (ALGOS & GH_SHA1) {
         uint32_t d[5];
@@ -233,8 +232,19 @@ __device__ __forceinline__ void load_block_direct(const uint8_t* p, uint32_t (&r
     }
 }
 
+// One 64-byte block of this lane's row out of a 128B-swizzled tile: 16-byte chunk c of row r sits at
+// chunk (c ^ (r & 7)). Shared-space addresses are 32-bit, so no generic-address arithmetic per load.
+__device__ __forceinline__ void lds_block(uint32_t row_addr, uint32_t c0, uint32_t sw, uint32_t (&q)[16]) {
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(q[4 * c]), "=r"(q[4 * c + 1]), "=r"(q[4 * c + 2]), "=r"(q[4 * c + 3])
+                     : "r"(row_addr + (((c0 + c) ^ sw) << 4))
+                     : "memory");
+}
+
 // ---------------------------------------------------------------------------- the hasher
-template <int ALGOS, bool STAGED>
+template <int ALGOS, bool STAGED, bool FMA, int TPS>
 __global__ void __launch_bounds__(32 * kMaxWarpsPerBlock)
 gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -255,15 +265,18 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     const uint32_t rem = ends_now ? static_cast<uint32_t>(avail & 63u) : 0u;
     const uint8_t* src = job.data + m * job.stride;
 
-    Lane<ALGOS> L;
+    Lane<ALGOS, FMA> L;
+    L.one = job.one;
     if (!done_before) {
         if (job.prior == 0) L.init();
         else L.load(job.state, job.n_msgs, m);
     }
 
     if constexpr (STAGED) {
-        uint8_t* tiles = smem + warp * kWarpSmem;
-        const uint32_t tiles_u32 = smem_u32(tiles);
+        constexpr uint32_t kChunk = TPS * kTileRowBytes;   // bytes of every message per stage
+        constexpr uint32_t kBPS = kChunk / 64;             // blocks per stage
+        constexpr uint32_t kWarpSmem = warp_smem(TPS);
+        const uint32_t tiles_u32 = smem_u32(smem + warp * kWarpSmem);
         const uint32_t bar0 = smem_u32(smem + wpb * kWarpSmem) + warp * (8 * kStages);
         if (lane == 0) {
 #pragma unroll
@@ -272,9 +285,7 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
         }
         __syncwarp();
 
-        constexpr uint32_t kBlocksPerStage = kChunk / 64;
-        const uint32_t my_stages = (nfull + kBlocksPerStage - 1) / kBlocksPerStage;
-        const uint32_t n_stages = __reduce_max_sync(0xffffffffu, my_stages);
+        const uint32_t n_stages = (__reduce_max_sync(0xffffffffu, nfull) + kBPS - 1) / kBPS;  // warp-uniform
         const uint32_t row0 = static_cast<uint32_t>(m_warp);  // tensor row of lane 0's message
 
         // one lane arms the stage barrier with the bytes of the boxes it is about to request
@@ -283,42 +294,32 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
             const uint32_t bar = bar0 + 8 * b;
             uint32_t ntile = 0;
 #pragma unroll
-            for (uint32_t t = 0; t < kTilesPerStage; t++)
+            for (uint32_t t = 0; t < TPS; t++)
                 if ((s * kChunk + t * kTileRowBytes) / 4 < job.tma_inner) ntile++;
             mbar_arrive_expect_tx(bar, ntile * kTileBytes);
 #pragma unroll
-            for (uint32_t t = 0; t < kTilesPerStage; t++) {
+            for (uint32_t t = 0; t < TPS; t++) {
                 const uint32_t x = (s * kChunk + t * kTileRowBytes) / 4;
-                if (x < job.tma_inner)
-                    tma_load_box(tiles_u32 + (b * kTilesPerStage + t) * kTileBytes, &tmap, x, row0, bar);
+                if (x < job.tma_inner) tma_load_box(tiles_u32 + (b * TPS + t) * kTileBytes, &tmap, x, row0, bar);
             }
         };
-
         if (lane == 0)
             for (uint32_t s = 0; s < kStages && s < n_stages; s++) issue(s);
 
-        // 128B swizzle: 16-byte chunk c of row r sits at chunk (c ^ (r & 7)) of that row
-        const uint32_t row_off = lane * kTileRowBytes;
+        const uint32_t row_base = tiles_u32 + lane * kTileRowBytes;
         const uint32_t sw = lane & 7u;
         for (uint32_t s = 0; s < n_stages; s++) {
             const uint32_t b = s % kStages;
             mbar_wait(bar0 + 8 * b, (s / kStages) & 1u);
-            const uint32_t first = s * kBlocksPerStage;
-            const uint32_t nb = nfull > first ? min(kBlocksPerStage, nfull - first) : 0u;
+            const uint32_t first = s * kBPS;
+            const uint32_t nb = nfull > first ? min(kBPS, nfull - first) : 0u;
 #pragma unroll 1
             for (uint32_t j = 0; j < nb; j++) {
-                const uint8_t* tile = tiles + (b * kTilesPerStage + (j >> 1)) * kTileBytes + row_off;
-                const uint32_t c0 = (j & 1u) * 4u;
-                const uint4 q0 = *reinterpret_cast<const uint4*>(tile + (((c0 + 0) ^ sw) << 4));
-                const uint4 q1 = *reinterpret_cast<const uint4*>(tile + (((c0 + 1) ^ sw) << 4));
-                const uint4 q2 = *reinterpret_cast<const uint4*>(tile + (((c0 + 2) ^ sw) << 4));
-                const uint4 q3 = *reinterpret_cast<const uint4*>(tile + (((c0 + 3) ^ sw) << 4));
-                const uint32_t r[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w,
-                                        q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
+                uint32_t r[16];
+                lds_block(row_base + (b * TPS + (j >> 1)) * kTileBytes, (j & 1u) * 4u, sw, r);
                 L.absorb(r);
             }
-            // every lane has consumed its row of buffer b (all LDS results were used above): the
-            // buffer can go back to the TMA unit for stage s + kStages
+            // every lane has consumed its row of buffer b: hand it back to the TMA unit for stage s+kStages
             __syncwarp();
             if (lane == 0 && s + kStages < n_stages) issue(s + kStages);
         }
@@ -334,8 +335,8 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     bool ok = false;
     if (!done_before) {
         if (ends_now) {
-            finalize<ALGOS>(L, src + static_cast<uint64_t>(nfull) * 64, rem, total_m);
-            ok = emit<ALGOS>(L, job, m);
+            finalize<ALGOS, FMA>(L, src + static_cast<uint64_t>(nfull) * 64, rem, total_m);
+            ok = emit<ALGOS, FMA>(L, job, m);
         } else {
             L.store(job.state, job.n_msgs, m);
         }
@@ -348,6 +349,302 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
             const uint32_t sh = static_cast<uint32_t>(bit0 & 31u);
             atomicOr(job.ok_words + (bit0 >> 5), okmask << sh);
             if (sh && (okmask >> (32 - sh))) atomicOr(job.ok_words + (bit0 >> 5) + 1, okmask >> (32 - sh));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------- role-split hasher
+// For batches with too few messages to give every sub-partition a warp (BASELINE configs 1-4 are all
+// like that: 4 096 / 12 800 / 320 / 3 073 messages on 592 sub-partitions), a lone warp runs at the
+// rate one ALU pipe issues it -- ~1 140 cycles per SHA-1 block, ~2 700 per SHA-256 block -- and idle
+// lanes or idle sub-partitions do not help (measured: profiles/). What does help is taking the part
+// of a block that does not depend on the chaining state off the chain's warp: the message schedule
+// (byte swap, W[16..] expansion, + K[t]) is ~40 % of SHA-1's and ~45 % of SHA-256's instructions.
+// So here 32 messages are served by a CTA of two (three) warps on different sub-partitions:
+//   warp S  "schedule": drives the TMA ring, reads the raw block, expands W, adds K and stores the
+//           round inputs WK[t] into a shared-memory buffer (one STS.128 per 4 rounds, conflict-free);
+//   warp R  "rounds":   owns the chaining state, reads WK[t] and runs only the rounds;
+//   warp M  (fused MD5+SHA-256 only): MD5 over the same TMA tiles.
+// Hand-off is by mbarrier pairs (full/empty) on two WK buffers and on the TMA stages.
+constexpr int kSplitStages = 3;
+constexpr int kSplitTPS = 2;
+constexpr uint32_t kSplitChunk = kSplitTPS * kTileRowBytes;
+constexpr uint32_t kSplitBPS = kSplitChunk / 64;
+template <int ALGO>
+struct SplitCfg {
+    static constexpr int kWords = ALGO == GH_SHA1 ? 80 : 64;       // round inputs per block
+    static constexpr int kWkBytes = kWords * 32 * 4;                // one WK buffer: [word/4][lane][4]
+};
+template <int ALGO>
+__host__ __device__ constexpr int split_smem() {
+    return kSplitStages * kSplitTPS * kTileBytes + 2 * SplitCfg<ALGO>::kWkBytes + 128;
+}
+
+__device__ __forceinline__ uint32_t sha1_k(int t) {
+    return t < 20 ? 0x5a827999u : t < 40 ? 0x6ed9eba1u : t < 60 ? 0x8f1bbcdcu : 0xca62c1d6u;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mbar_arrive1(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// SHA-1 rounds over precomputed WK[t] = W[t] + K[t] (FIPS 180-4 6.1.2 step 3 without the schedule)
+// `one` (the kernel parameter 1) makes e + WK an IMAD that ptxas can neither fold nor re-associate:
+// that sum is ready rounds ahead, and keeping it a separate operand leaves exactly one dependent
+// instruction (LEA.HI = rotl5(a) + t) between consecutive values of a.
+__device__ __forceinline__ void sha1_rounds(uint32_t (&s)[5], uint32_t wk_addr, uint32_t one) {
+    uint32_t a = s[0], b = s[1], c = s[2], d = s[3], e = s[4];
+    uint4 v[3];
+    v[0] = lds128(wk_addr);
+    v[1] = lds128(wk_addr + 512);
+    v[2] = lds128(wk_addr + 1024);
+#pragma unroll
+    for (int ch = 0; ch < 20; ch++) {
+        const uint4 cur = v[ch % 3];
+        if (ch + 3 < 20) v[ch % 3] = lds128(wk_addr + (ch + 3) * 512);
+        const uint32_t wk[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int t = 4 * ch + i;
+            uint32_t f;
+            if (t < 20) f = f_ch(b, c, d);
+            else if (t < 40) f = f_xor3(b, c, d);
+            else if (t < 60) f = f_maj(b, c, d);
+            else f = f_xor3(b, c, d);
+            const uint32_t pre = addf<true>(e, wk[i], one);
+            const uint32_t tmp = rotl(a, 5) + (f + pre);
+            e = d; d = c; c = rotl(b, 30); b = a; a = tmp;
+        }
+    }
+    s[0] += a; s[1] += b; s[2] += c; s[3] += d; s[4] += e;
+}
+
+__device__ __forceinline__ void sha256_rounds(uint32_t (&s)[8], uint32_t wk_addr, uint32_t one) {
+    uint32_t x[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = s[i];
+    uint4 v[3];
+    v[0] = lds128(wk_addr);
+    v[1] = lds128(wk_addr + 512);
+    v[2] = lds128(wk_addr + 1024);
+#pragma unroll
+    for (int ch = 0; ch < 16; ch++) {
+        const uint4 cur = v[ch % 3];
+        if (ch + 3 < 16) v[ch % 3] = lds128(wk_addr + (ch + 3) * 512);
+        const uint32_t wk[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int t = 4 * ch + i;
+            uint32_t& a = x[(0 - t) & 7]; uint32_t& b = x[(1 - t) & 7]; uint32_t& c = x[(2 - t) & 7];
+            uint32_t& d = x[(3 - t) & 7]; uint32_t& e = x[(4 - t) & 7]; uint32_t& f = x[(5 - t) & 7];
+            uint32_t& g = x[(6 - t) & 7]; uint32_t& h = x[(7 - t) & 7];
+            // h + WK is ready rounds ahead (IMAD, not re-associable); Sigma1(e), the deepest term, is added last
+            const uint32_t hk = addf<true>(h, wk[i], one);
+            const uint32_t xc = hk + f_ch(e, f, g);
+            const uint32_t s1e = S256_S1(e);
+            const uint32_t t2 = S256_S0(a) + f_maj(a, b, c);
+            d = (d + xc) + s1e;
+            h = (xc + t2) + s1e;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) s[i] += x[i];
+}
+
+// schedule warp: w = the block as big-endian-decoded words; writes WK[0..kWords) for its lane
+template <int ALGO>
+__device__ __forceinline__ void expand_and_store(uint32_t (&w)[16], uint32_t wk_addr) {
+    uint32_t o[4];
+    if constexpr (ALGO == GH_SHA1) {
+#pragma unroll
+        for (int t = 0; t < 80; t++) {
+            uint32_t wt;
+            if (t < 16) wt = w[t];
+            else { wt = rotl(f_xor3(w[(t - 3) & 15], w[(t - 8) & 15], w[(t - 14) & 15]) ^ w[t & 15], 1); w[t & 15] = wt; }
+            o[t & 3] = wt + sha1_k(t);
+            if ((t & 3) == 3) sts128(wk_addr + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
+        }
+    } else {
+#pragma unroll
+        for (int t = 0; t < 64; t++) {
+            uint32_t wt;
+            if (t < 16) wt = w[t];
+            else {
+                wt = S256_s1(w[(t - 2) & 15]) + w[(t - 7) & 15] + S256_s0(w[(t - 15) & 15]) + w[t & 15];
+                w[t & 15] = wt;
+            }
+            o[t & 3] = wt + K256[t];
+            if ((t & 3) == 3) sts128(wk_addr + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
+template <int ALGO, bool WITH_MD5>
+__global__ void __launch_bounds__(WITH_MD5 ? 96 : 64)
+gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    using Cfg = SplitCfg<ALGO>;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t role = threadIdx.x >> 5;  // 0 = rounds, 1 = schedule, 2 = MD5
+    const uint64_t m_warp = job.first_msg + static_cast<uint64_t>(blockIdx.x) * 32u;
+    const uint64_t m = m_warp + lane;
+    const bool active = m < job.first_msg + job.count;
+
+    // Every message this grid covers has the same number of bytes present in this launch (the launcher
+    // excludes a last message with fewer), so trip counts are uniform across the CTA; whether a
+    // message ENDS in this launch is still a per-lane matter (the last one may be shorter overall).
+    const uint64_t common_remain = job.prior >= job.msg_len ? 0 : job.msg_len - job.prior;
+    const uint32_t n_blocks = static_cast<uint32_t>((common_remain < job.chunk_len ? common_remain : job.chunk_len) >> 6);
+    const uint32_t n_stages = (n_blocks + kSplitBPS - 1) / kSplitBPS;
+    const uint64_t total_m = m == job.n_msgs - 1 ? job.last_msg_len : job.msg_len;
+    const bool done_before = job.prior > 0 && job.prior >= total_m;
+    const uint64_t remain = done_before ? 0 : total_m - job.prior;
+    const bool ends_now = !done_before && remain <= job.chunk_len;
+    const uint64_t avail = remain < job.chunk_len ? remain : job.chunk_len;
+    const uint32_t rem = ends_now ? static_cast<uint32_t>(avail & 63u) : 0u;
+    const uint8_t* src = job.data + m * job.stride;
+
+    const uint32_t tiles_u32 = smem_u32(smem);
+    const uint32_t wk_u32 = tiles_u32 + kSplitStages * kSplitTPS * kTileBytes;
+    const uint32_t bars = wk_u32 + 2 * Cfg::kWkBytes;
+    const uint32_t tma_full = bars, tma_empty = bars + 8 * kSplitStages;
+    const uint32_t w_full = bars + 16 * kSplitStages, w_empty = w_full + 16;
+    constexpr uint32_t kTileReaders = WITH_MD5 ? 2 : 1;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kSplitStages; s++) {
+            mbar_init(tma_full + 8 * s, 1);
+            mbar_init(tma_empty + 8 * s, kTileReaders);
+        }
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            mbar_init(w_full + 8 * b, 1);
+            mbar_init(w_empty + 8 * b, 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();  // the only CTA-wide barrier: after this the warps meet through mbarriers only
+
+    const uint32_t row_base = tiles_u32 + lane * kTileRowBytes;
+    const uint32_t sw = lane & 7u;
+
+    if (role == 1) {
+        // ------------------------------------------------------------------ schedule warp
+        const uint32_t row0 = static_cast<uint32_t>(m_warp);
+        auto issue = [&](uint32_t s) {
+            const uint32_t b = s % kSplitStages;
+            uint32_t ntile = 0;
+#pragma unroll
+            for (uint32_t t = 0; t < kSplitTPS; t++)
+                if ((s * kSplitChunk + t * kTileRowBytes) / 4 < job.tma_inner) ntile++;
+            mbar_arrive_expect_tx(tma_full + 8 * b, ntile * kTileBytes);
+#pragma unroll
+            for (uint32_t t = 0; t < kSplitTPS; t++) {
+                const uint32_t x = (s * kSplitChunk + t * kTileRowBytes) / 4;
+                if (x < job.tma_inner)
+                    tma_load_box(tiles_u32 + (b * kSplitTPS + t) * kTileBytes, &tmap, x, row0, tma_full + 8 * b);
+            }
+        };
+        if (lane == 0)
+            for (uint32_t s = 0; s < kSplitStages && s < n_stages; s++) issue(s);
+        uint32_t jb = 0;
+        for (uint32_t s = 0; s < n_stages; s++) {
+            const uint32_t b = s % kSplitStages;
+            mbar_wait(tma_full + 8 * b, (s / kSplitStages) & 1u);
+            const uint32_t nb = min(kSplitBPS, n_blocks - s * kSplitBPS);
+#pragma unroll 1
+            for (uint32_t j = 0; j < nb; j++, jb++) {
+                uint32_t r[16], w[16];
+                lds_block(row_base + (b * kSplitTPS + (j >> 1)) * kTileBytes, (j & 1u) * 4u, sw, r);
+#pragma unroll
+                for (int i = 0; i < 16; i++) w[i] = bswap(r[i]);
+                const uint32_t wb = jb & 1u, use = jb >> 1;
+                if (use) mbar_wait(w_empty + 8 * wb, (use - 1) & 1u);  // rounds warp has drained this buffer
+                expand_and_store<ALGO>(w, wk_u32 + wb * Cfg::kWkBytes + lane * 16);
+                __syncwarp();  // orders every lane's stores before lane 0's release-arrive
+                if (lane == 0) mbar_arrive1(w_full + 8 * wb);
+            }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive1(tma_empty + 8 * b);
+                if (s + kSplitStages < n_stages) {
+                    mbar_wait(tma_empty + 8 * b, (s / kSplitStages) & 1u);  // the MD5 warp is done with it too
+                    issue(s + kSplitStages);
+                }
+            }
+        }
+    } else if (role == 0) {
+        // ------------------------------------------------------------------ rounds warp
+        Lane<ALGO, false> L;
+        L.one = 1;
+        if (!done_before) {
+            if (job.prior == 0) L.init();
+            else if (active) L.load(job.state, job.n_msgs, m);
+        }
+#pragma unroll 1
+        for (uint32_t jb = 0; jb < n_blocks; jb++) {
+            const uint32_t wb = jb & 1u, use = jb >> 1;
+            mbar_wait(w_full + 8 * wb, use & 1u);
+            const uint32_t wk_addr = wk_u32 + wb * Cfg::kWkBytes + lane * 16;
+            if constexpr (ALGO == GH_SHA1) sha1_rounds(L.s1, wk_addr, job.one);
+            else sha256_rounds(L.s2, wk_addr, job.one);
+            __syncwarp();
+            if (lane == 0) mbar_arrive1(w_empty + 8 * wb);
+        }
+        bool ok = false;
+        if (active && !done_before) {
+            if (ends_now) {
+                finalize<ALGO, false>(L, src + static_cast<uint64_t>(n_blocks) * 64, rem, total_m);
+                ok = emit<ALGO, false>(L, job, m);
+            } else {
+                L.store(job.state, job.n_msgs, m);
+            }
+        }
+        __syncwarp();
+        if (job.ok_words) {
+            const uint32_t okmask = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0 && okmask) {
+                const uint64_t bit0 = job.ok_base + m;
+                const uint32_t sh = static_cast<uint32_t>(bit0 & 31u);
+                atomicOr(job.ok_words + (bit0 >> 5), okmask << sh);
+                if (sh && (okmask >> (32 - sh))) atomicOr(job.ok_words + (bit0 >> 5) + 1, okmask >> (32 - sh));
+            }
+        }
+    } else if (WITH_MD5) {
+        // ------------------------------------------------------------------ MD5 warp
+        Lane<GH_MD5, false> L;
+        L.one = 1;
+        if (!done_before) {
+            if (job.prior == 0) L.init();
+            else if (active) L.load(job.state, job.n_msgs, m);
+        }
+        for (uint32_t s = 0; s < n_stages; s++) {
+            const uint32_t b = s % kSplitStages;
+            mbar_wait(tma_full + 8 * b, (s / kSplitStages) & 1u);
+            const uint32_t nb = min(kSplitBPS, n_blocks - s * kSplitBPS);
+#pragma unroll 1
+            for (uint32_t j = 0; j < nb; j++) {
+                uint32_t r[16];
+                lds_block(row_base + (b * kSplitTPS + (j >> 1)) * kTileBytes, (j & 1u) * 4u, sw, r);
+                L.absorb(r);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive1(tma_empty + 8 * b);
+        }
+        if (active && !done_before) {
+            if (ends_now) {
+                finalize<GH_MD5, false>(L, src + static_cast<uint64_t>(n_blocks) * 64, rem, total_m);
+                emit<GH_MD5, false>(L, job, m);
+            } else {
+                L.store(job.state, job.n_msgs, m);
+            }
         }
     }
 }
@@ -410,24 +707,77 @@ bool make_tmap(const GhJob& job, uint64_t rows, uint64_t inner_words, CUtensorMa
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Tuning switches (read once): GPUHASH_FMA_ADDS=0 keeps every add on the ALU pipe, GPUHASH_TPS=2|4
+// forces the stage depth. Defaults are what measured best on B200 (profiles/).
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+// -1 = per-algorithm default (measured): SHA-1 keeps its adds on the ALU pipe (the FMA hop lengthens the
+// lone-warp chain by 17 % and buys 1 % when saturated), SHA-256 moves them (+12..15 %), fused
+// MD5+SHA-256 moves them only when warps are plentiful.
+int fma_adds_override() {
+    static const int v = env_int("GPUHASH_FMA_ADDS", -1);
+    return v;
+}
+// Role-split kernels are used while message-warps <= this many per SM (0 disables). Measured on B200:
+// at 64..128 message-warps the split is +27..48 %; at 400 (2.7 per SM) its 800 warps oversubscribe the
+// 592 sub-partitions and it loses 7 %, so the default is 2 per SM = one warp per sub-partition.
+int split_max_warps_per_sm() {
+    static const int v = env_int("GPUHASH_SPLIT_WARPS_PER_SM", 2);
+    return v;
+}
+int forced_tps() {
+    static const int v = env_int("GPUHASH_TPS", 0);
+    return v;
+}
+
+template <int ALGOS, bool FMA, int TPS>
+cudaError_t launch_staged(const GhJob& job, const CUtensorMap& tmap, unsigned blocks, int wpb, cudaStream_t stream) {
+    const size_t smem = static_cast<size_t>(wpb) * (warp_smem(TPS) + 8 * kStages);
+    gh_hash_lanes<ALGOS, true, FMA, TPS><<<dim3(blocks), dim3(32 * wpb), smem, stream>>>(tmap, job);
+    return cudaGetLastError();
+}
+
+template <int ALGO, bool WITH_MD5>
+cudaError_t launch_split(const GhJob& job_in, uint64_t count, const CUtensorMap& tmap, uint32_t inner_words,
+                         cudaStream_t stream) {
+    GhJob job = job_in;
+    job.first_msg = 0;
+    job.count = count;
+    job.tma_inner = inner_words;
+    job.one = 1;
+    const uint64_t nblocks = (count + 31) / 32;
+    if (nblocks > 0x7fffffffull) return cudaErrorInvalidValue;
+    gh_hash_split<ALGO, WITH_MD5><<<dim3(static_cast<unsigned>(nblocks)), dim3(WITH_MD5 ? 96 : 64), split_smem<ALGO>(),
+                                    stream>>>(tmap, job);
+    return cudaGetLastError();
+}
+
 template <int ALGOS>
 cudaError_t launch_range(const GhJob& job_in, uint64_t first, uint64_t count, bool staged, const CUtensorMap& tmap,
-                         uint32_t inner_words, int wpb, cudaStream_t stream) {
+                         uint32_t inner_words, int wpb, int tps, cudaStream_t stream) {
     if (count == 0) return cudaSuccess;
     GhJob job = job_in;
     job.first_msg = first;
     job.count = count;
     job.tma_inner = inner_words;
+    job.one = 1;
     const uint64_t warps = (count + 31) / 32;
-    const uint64_t blocks = (warps + wpb - 1) / wpb;
-    if (blocks > 0x7fffffffull) return cudaErrorInvalidValue;
-    const dim3 grid(static_cast<unsigned>(blocks)), block(32 * wpb);
+    const uint64_t nblocks = (warps + wpb - 1) / wpb;
+    if (nblocks > 0x7fffffffull) return cudaErrorInvalidValue;
+    const unsigned blocks = static_cast<unsigned>(nblocks);
+    bool fma = ALGOS == GH_SHA256 || (ALGOS == (GH_MD5 | GH_SHA256) && wpb > 1);
+    if (ALGOS == GH_MD5) fma = false;  // MD5 has no FMA variant
+    if (fma_adds_override() >= 0 && ALGOS != GH_MD5) fma = fma_adds_override() != 0;
     if (staged) {
-        const size_t smem = static_cast<size_t>(wpb) * (kWarpSmem + 8 * kStages);
-        gh_hash_lanes<ALGOS, true><<<grid, block, smem, stream>>>(tmap, job);
-    } else {
-        gh_hash_lanes<ALGOS, false><<<grid, block, 0, stream>>>(tmap, job);
+        if (fma) return tps == 4 ? launch_staged<ALGOS, true, 4>(job, tmap, blocks, wpb, stream)
+                                 : launch_staged<ALGOS, true, 2>(job, tmap, blocks, wpb, stream);
+        return tps == 4 ? launch_staged<ALGOS, false, 4>(job, tmap, blocks, wpb, stream)
+                        : launch_staged<ALGOS, false, 2>(job, tmap, blocks, wpb, stream);
     }
+    if (fma) gh_hash_lanes<ALGOS, false, true, 2><<<dim3(blocks), dim3(32 * wpb), 0, stream>>>(tmap, job);
+    else gh_hash_lanes<ALGOS, false, false, 2><<<dim3(blocks), dim3(32 * wpb), 0, stream>>>(tmap, job);
     return cudaGetLastError();
 }
 
@@ -450,27 +800,58 @@ cudaError_t launch_algo(const GhJob& job, int sm_count, cudaStream_t stream) {
     memset(&tmap, 0, sizeof(tmap));
     bool staged = aligned && inner_words > 0 && inner_words <= 0xffffffffull && tma_rows > 0 &&
                   tma_rows <= 0xffffffffull && make_tmap(job, tma_rows, inner_words, &tmap);
-    // few messages: one warp per block so that warps spread over all SMs / sub-partitions;
-    // many messages: 4 warps per block (one per sub-partition) to stay under the 32 blocks/SM limit
+    // few messages: one warp per block so that warps spread over all SMs / sub-partitions, deep stages;
+    // many messages: 4 warps per block (one per sub-partition), shallow stages so 13 warps fit an SM
     const uint64_t warps = (job.n_msgs + 31) / 32;
-    const int wpb = warps > static_cast<uint64_t>(sm_count > 0 ? sm_count : 148) * 8 ? kMaxWarpsPerBlock : 1;
+    const uint64_t sms = static_cast<uint64_t>(sm_count > 0 ? sm_count : 148);
+    const int wpb = warps > sms * 8 ? kMaxWarpsPerBlock : 1;
+    int tps = warps > sms * 6 ? 2 : 4;
+    if (forced_tps() == 2 || forced_tps() == 4) tps = forced_tps();
     cudaError_t e;
-    if (staged) {
-        e = launch_range<ALGOS>(job, 0, tma_rows, true, tmap, static_cast<uint32_t>(inner_words), wpb, stream);
+    if (staged && ALGOS != GH_MD5 && warps <= sms * static_cast<uint64_t>(split_max_warps_per_sm())) {
+        // too few chains to fill the machine: spend the idle sub-partitions on the message schedule
+        if constexpr (ALGOS == GH_SHA1) e = launch_split<GH_SHA1, false>(job, tma_rows, tmap, static_cast<uint32_t>(inner_words), stream);
+        else if constexpr (ALGOS == GH_SHA256) e = launch_split<GH_SHA256, false>(job, tma_rows, tmap, static_cast<uint32_t>(inner_words), stream);
+        else if constexpr (ALGOS == (GH_MD5 | GH_SHA256)) e = launch_split<GH_SHA256, true>(job, tma_rows, tmap, static_cast<uint32_t>(inner_words), stream);
+        else e = cudaErrorInvalidValue;
         if (e != cudaSuccess) return e;
-        if (last_short) e = launch_range<ALGOS>(job, job.n_msgs - 1, 1, false, tmap, 0, 1, stream);
+        if (last_short) e = launch_range<ALGOS>(job, job.n_msgs - 1, 1, false, tmap, 0, 1, tps, stream);
         return e;
     }
-    return launch_range<ALGOS>(job, 0, job.n_msgs, false, tmap, 0, wpb, stream);
+    if (staged) {
+        e = launch_range<ALGOS>(job, 0, tma_rows, true, tmap, static_cast<uint32_t>(inner_words), wpb, tps, stream);
+        if (e != cudaSuccess) return e;
+        if (last_short) e = launch_range<ALGOS>(job, job.n_msgs - 1, 1, false, tmap, 0, 1, tps, stream);
+        return e;
+    }
+    return launch_range<ALGOS>(job, 0, job.n_msgs, false, tmap, 0, wpb, tps, stream);
+}
+
+template <int ALGOS, bool FMA, int TPS>
+cudaError_t init_one() {
+    cudaError_t e = cudaFuncSetAttribute(gh_hash_lanes<ALGOS, true, FMA, TPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kMaxWarpsPerBlock * (warp_smem(TPS) + 8 * kStages));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(gh_hash_lanes<ALGOS, true, FMA, TPS>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
+}
+
+template <int ALGO, bool WITH_MD5>
+cudaError_t init_split() {
+    cudaError_t e = cudaFuncSetAttribute(gh_hash_split<ALGO, WITH_MD5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         split_smem<ALGO>());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(gh_hash_split<ALGO, WITH_MD5>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
 }
 
 template <int ALGOS>
 cudaError_t init_algo() {
-    cudaError_t e = cudaFuncSetAttribute(gh_hash_lanes<ALGOS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kMaxWarpsPerBlock * (kWarpSmem + 8 * kStages));
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(gh_hash_lanes<ALGOS, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                cudaSharedmemCarveoutMaxShared);
+    cudaError_t e;
+    if ((e = init_one<ALGOS, true, 2>()) != cudaSuccess) return e;
+    if ((e = init_one<ALGOS, true, 4>()) != cudaSuccess) return e;
+    if ((e = init_one<ALGOS, false, 2>()) != cudaSuccess) return e;
+    return init_one<ALGOS, false, 4>();
 }
 
 }  // namespace
@@ -481,6 +862,9 @@ cudaError_t gh_kernels_init_device() {
     if ((e = init_algo<GH_MD5>()) != cudaSuccess) return e;
     if ((e = init_algo<GH_SHA256>()) != cudaSuccess) return e;
     if ((e = init_algo<GH_MD5 | GH_SHA256>()) != cudaSuccess) return e;
+    if ((e = init_split<GH_SHA1, false>()) != cudaSuccess) return e;
+    if ((e = init_split<GH_SHA256, false>()) != cudaSuccess) return e;
+    if ((e = init_split<GH_SHA256, true>()) != cudaSuccess) return e;
     return encode_tiled() ? cudaSuccess : cudaErrorNotSupported;
 }
 

@@ -20,9 +20,9 @@
         }                                                                             \
     } while (0)
 
-enum { OP_IADD3, OP_LOP3, OP_SHF, OP_PRMT, OP_IMAD, OP_LOP3_IMAD, OP_ALU_MIX, OP_SHA1, OP_MD5, OP_SHA256, OP_COUNT };
+enum { OP_IADD3, OP_LOP3, OP_SHF, OP_PRMT, OP_IMAD, OP_LOP3_IMAD, OP_ALU_MIX, OP_SHA1, OP_MD5, OP_SHA256, OP_SHA1_FMA, OP_SHA256_FMA, OP_COUNT };
 static const char* kNames[OP_COUNT] = {"iadd3", "lop3", "shf", "prmt", "imad", "lop3+imad", "shf+lop3+iadd3",
-                                       "sha1_block", "md5_block", "sha256_block"};
+                                       "sha1_block", "md5_block", "sha256_block", "sha1_block_fma_adds", "sha256_block_fma_adds"};
 
 template <int OP>
 __device__ __forceinline__ void body(uint32_t (&x)[8], uint32_t a, uint32_t b) {
@@ -67,7 +67,8 @@ __global__ void k_ops(uint32_t* out, uint32_t a, uint32_t b, int iters, long lon
 
 // whole compression functions on register-resident data: cycles per 64-byte block per warp
 template <int OP>
-__global__ void k_hash(uint32_t* out, uint32_t a, int iters, long long* cycles) {
+__global__ void k_hash(uint32_t* out, uint32_t a, int iters, long long* cycles, uint32_t one, uint32_t lane_mask) {
+    if (!((lane_mask >> (threadIdx.x & 31)) & 1)) return;  // partially filled warps: does the pipe skip idle halves?
     uint32_t w[16];
 #pragma unroll
     for (int i = 0; i < 16; i++) w[i] = threadIdx.x * 16 + i + a;
@@ -75,7 +76,6 @@ __global__ void k_hash(uint32_t* out, uint32_t a, int iters, long long* cycles) 
     ghd::sha1_init(s1);
     ghd::md5_init(m5);
     ghd::sha256_init(s2);
-    __syncthreads();
     const long long t0 = clock64();
     for (int it = 0; it < iters; it++) {
         uint32_t v[16];
@@ -84,6 +84,8 @@ __global__ void k_hash(uint32_t* out, uint32_t a, int iters, long long* cycles) 
         if (OP == OP_SHA1) ghd::sha1_compress(s1, v);
         if (OP == OP_MD5) ghd::md5_compress(m5, v);
         if (OP == OP_SHA256) ghd::sha256_compress(s2, v);
+        if (OP == OP_SHA1_FMA) ghd::sha1_compress<true>(s1, v, one);
+        if (OP == OP_SHA256_FMA) ghd::sha256_compress<true>(s2, v, one);
     }
     const long long t1 = clock64();
     uint32_t s = 0;
@@ -94,9 +96,10 @@ __global__ void k_hash(uint32_t* out, uint32_t a, int iters, long long* cycles) 
     if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
 }
 
+static uint32_t g_lane_mask = 0xffffffffu;
 template <int OP>
 static double run_ops(int sms, int threads, uint32_t* d_out, long long* d_cyc, int iters) {
-    if (OP >= OP_SHA1) k_hash<OP><<<sms, threads>>>(d_out, 3, iters, d_cyc);
+    if (OP >= OP_SHA1) k_hash<OP><<<sms, threads>>>(d_out, 3, iters, d_cyc, 1, g_lane_mask);
     else k_ops<OP><<<sms, threads>>>(d_out, 0x9e3779b9u, 0x7f4a7c15u, iters, d_cyc);
     CK(cudaDeviceSynchronize());
     std::vector<long long> cyc(sms);
@@ -150,7 +153,17 @@ int main(int argc, char** argv) {
     printf(" },\n \"compress_by_threads_per_sm\": {\n");
     report<OP_SHA1>(sms, d_out, d_cyc, false);
     report<OP_MD5>(sms, d_out, d_cyc, false);
+    report<OP_SHA256>(sms, d_out, d_cyc, false);
+    report<OP_SHA1_FMA>(sms, d_out, d_cyc, false);
+    report<OP_SHA256_FMA>(sms, d_out, d_cyc, true);
+    printf(" },\n \"compress_16_of_32_lanes_active\": {\n");
+    g_lane_mask = 0x0000ffffu;
+    report<OP_SHA1>(sms, d_out, d_cyc, false);
     report<OP_SHA256>(sms, d_out, d_cyc, true);
+    printf(" },\n \"compress_8_of_32_lanes_active\": {\n");
+    g_lane_mask = 0x000000ffu;
+    report<OP_SHA1>(sms, d_out, d_cyc, true);
+    g_lane_mask = 0xffffffffu;
     printf(" },\n");
 
     // ---- host -> device link

@@ -24,7 +24,7 @@ DIGEST_LEN = {SHA1: 20, MD5: 16, SHA256: 32}
 GH_OK, GH_EINVAL, GH_ENODEVICE, GH_ENOMEM, GH_ECUDA, GH_ECTX_LOST, GH_ERANGE = range(7)
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "libgpuhash.so")
+LIB_PATH = os.environ.get("GPUHASH_LIB") or os.path.join(_PKG, "libgpuhash.so")
 
 
 class GpuHashError(RuntimeError):

@@ -337,3 +337,18 @@ def test_stats_report_launches_and_bytes(gh):
     assert after.h2d_bytes - before.h2d_bytes == (1 << 20)
     assert after.d2h_bytes - before.d2h_bytes == 64 * 20
     assert after.kernel_ms > 0
+
+
+def test_lane_kernels_with_role_split_disabled():
+    """Small batches normally take the role-split kernels (schedule / rounds / MD5 warps); the
+    library reads its tuning switches once per process, so the one-message-per-lane kernels are
+    exercised on the same cases in a child process with the split switched off."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, GPUHASH_SPLIT_WARPS_PER_SM="0")
+    here = os.path.abspath(__file__)
+    r = subprocess.run([sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k",
+                        "differential or chunk_interleaved or resumable or cfg5 or padding or cfg3"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
