@@ -2,8 +2,10 @@
 // host-span gather, multi-GPU sharding and the device-resident entry points.
 //
 // Host-side design: per device a ring of `slots` device buffers, each
-// with its own CUDA stream, so the H2D copies of slot b+1 run on the copy engine while the hashing
-// kernel of slot b runs on the SMs. Spans that already live in pinned memory are DMA'd straight from
+// with its own COPY stream, and one COMPUTE stream for every hashing kernel. A window's copies wait
+// for the kernel that last read the slot (event `consumed`), its kernel waits for the copies (event
+// `h2d_done`); so the H2D of windows b+1.. runs on the copy engine while the kernel of window b runs
+// on the SMs, and kernels are naturally ordered (they may share midstates). Spans that already live in pinned memory are DMA'd straight from
 // the caller's buffer; pageable spans are first copied into the slot's pinned mirror by a small host
 // thread pool. Pieces / parts are independent, so devices get contiguous 64-aligned message ranges and
 // there is no collective of any kind.
@@ -14,6 +16,7 @@
 #include <chrono>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <mutex>
@@ -27,7 +30,7 @@
 namespace {
 
 constexpr uint64_t kDefaultSlotBytes = 256ull << 20;
-constexpr int kDefaultSlots = 3;
+constexpr int kDefaultSlots = 4;
 constexpr int kDefaultStageThreads = 4;
 constexpr uint64_t kMinChunk = 64ull << 10;  // smallest per-message chunk of the chunk-interleaved mode
 
@@ -125,10 +128,12 @@ class Pool {
 
 struct Slot {
     uint8_t* d_buf = nullptr;
-    uint8_t* h_pin = nullptr;  // pinned mirror, allocated on first pageable span
-    cudaStream_t stream = nullptr;
-    cudaEvent_t h2d_done = nullptr;  // last H2D out of h_pin
+    uint8_t* h_pin = nullptr;        // pinned mirror, allocated on first pageable span
+    cudaStream_t stream = nullptr;   // copy stream of this slot
+    cudaEvent_t h2d_done = nullptr;  // the window's bytes are in d_buf (and h_pin may be refilled)
+    cudaEvent_t consumed = nullptr;  // the kernel reading d_buf has finished
     bool h2d_pending = false;
+    bool in_use = false;             // a kernel was queued on d_buf since the call started
 };
 
 struct Device {
@@ -143,7 +148,6 @@ struct Device {
     uint8_t* h_out = nullptr;   uint64_t h_out_cap = 0;   // pinned mirror of results
     std::vector<cudaEvent_t> ev_pool;                     // start/stop pairs for kernel timing
     size_t ev_used = 0;
-    cudaEvent_t chain = nullptr;                          // orders chunk j+1's kernel after chunk j's
 };
 
 }  // namespace
@@ -317,10 +321,18 @@ int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint
 int flush_staged(gh_ctx* c, Slot& s, uint64_t lo, uint64_t hi) {
     if (lo >= hi) return GH_OK;
     GH_CUDA(c, cudaMemcpyAsync(s.d_buf + lo, s.h_pin + lo, hi - lo, cudaMemcpyHostToDevice, s.stream));
-    GH_CUDA(c, cudaEventRecord(s.h2d_done, s.stream));
     s.h2d_pending = true;
     return GH_OK;
 }
+
+// Before a window's copies: the slot's previous kernel must have drained it.
+int slot_begin(gh_ctx* c, Slot& s) {
+    if (s.in_use) GH_CUDA(c, cudaStreamWaitEvent(s.stream, s.consumed, 0));
+    return GH_OK;
+}
+
+// After a window's copies: queue its kernel(s) on the compute stream behind them.
+int slot_launch(gh_ctx* c, Device& d, Slot& s, int algos, const GhJob& j);
 
 // Chunk-interleaved window: for every message m of the group [g0, g0+g) bring stream bytes
 // [(g0+m)*L + prior, +min(chunk, len_m - prior)) to slot offset m*chunk. Consecutive rows that lie
@@ -356,7 +368,13 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g
         }
         const uint8_t* src = static_cast<const uint8_t*>(ix.spans[si].host_ptr) + (lo - ix.start[si]);
         if (ix.pinned[si]) {
-            GH_CUDA(c, cudaMemcpy2DAsync(s.d_buf + m * chunk, chunk, src, L, w, rows, cudaMemcpyHostToDevice, s.stream));
+            static const bool no2d = getenv("GPUHASH_NO_2D") != nullptr;
+            if (no2d) {
+                for (uint64_t r = 0; r < rows; r++)
+                    GH_CUDA(c, cudaMemcpyAsync(s.d_buf + (m + r) * chunk, src + r * L, w, cudaMemcpyHostToDevice, s.stream));
+            } else {
+                GH_CUDA(c, cudaMemcpy2DAsync(s.d_buf + m * chunk, chunk, src, L, w, rows, cudaMemcpyHostToDevice, s.stream));
+            }
         } else {
             if (!s.h_pin) GH_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256));
             if (s.h2d_pending) {
@@ -371,6 +389,16 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g
         m += rows;
     }
     return flush_staged(c, s, st_lo, st_hi);
+}
+
+int slot_launch(gh_ctx* c, Device& d, Slot& s, int algos, const GhJob& j) {
+    GH_CUDA(c, cudaEventRecord(s.h2d_done, s.stream));
+    GH_CUDA(c, cudaStreamWaitEvent(d.stream, s.h2d_done, 0));
+    int rc = launch_window(c, d, algos, j, d.stream, true);
+    if (rc) return rc;
+    GH_CUDA(c, cudaEventRecord(s.consumed, d.stream));
+    s.in_use = true;
+    return GH_OK;
 }
 
 // --------------------------------------------------------------------------- one device's share
@@ -407,14 +435,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
         GH_CUDA(c, cudaMemcpyAsync(d.d_out + o_exp, d.h_out + o_exp, 20 * n, cudaMemcpyHostToDevice, d.stream));
         GH_CUDA(c, cudaMemsetAsync(d.d_ok, 0, (ok_words + 1) * 4, d.stream));
     }
-    cudaEvent_t prep;
-    {
-        EvPair ev;
-        if ((rc = next_events(c, d, &ev))) return rc;
-        prep = ev.a;
-        GH_CUDA(c, cudaEventRecord(prep, d.stream));
-        for (auto& s : d.slots) GH_CUDA(c, cudaStreamWaitEvent(s.stream, prep, 0));
-    }
+    for (auto& sl : d.slots) sl.in_use = false;
     const size_t first_timing_event = d.ev_used;
 
     GhJob job{};
@@ -435,6 +456,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
             const uint64_t k = std::min(per, m1 - q);
             const uint64_t lo = q * L, hi = std::min((q + k) * L, total);
             uint64_t st_lo = ~0ull, st_hi = 0;
+            if ((rc = slot_begin(c, s))) return rc;
             if ((rc = gather(c, *A.ix, lo, hi, s, 0, &st_lo, &st_hi))) return rc;
             if ((rc = flush_staged(c, s, st_lo, st_hi))) return rc;
             GhJob j = job;
@@ -453,17 +475,15 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
                 j.ok_words = d.d_ok;
                 j.ok_base = rel;
             }
-            if ((rc = launch_window(c, d, A.algos, j, s.stream, true))) return rc;
+            if ((rc = slot_launch(c, d, s, A.algos, j))) return rc;
         }
     } else {
         // chunk-interleaved: every window carries the next `chunk` bytes of every message of a group,
         // so that all chains advance together; midstates stay in HBM. Rows that
         // lie inside one pinned span travel as a single strided (2-D) DMA.
         if ((rc = grow(c, &d.d_state, &d.d_state_cap, n * GH_STATE_WORDS * 4))) return rc;
-        if (!d.chain) GH_CUDA(c, cudaEventCreateWithFlags(&d.chain, cudaEventDisableTiming));
         const uint64_t gsz = std::min<uint64_t>(n, std::max<uint64_t>(1, S / kMinChunk));
         uint64_t b = 0;
-        bool have_chain = false;
         for (uint64_t g0 = m0; g0 < m1; g0 += gsz) {
             const uint64_t g = std::min(gsz, m1 - g0);
             const uint64_t chunk = std::min<uint64_t>((S / g) & ~63ull, (L + 63) & ~63ull);
@@ -471,6 +491,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
             const uint64_t g_last_len = (g0 + g == A.n_total) ? last_len_global : L;
             for (uint64_t prior = 0; prior < L; prior += chunk, b++) {
                 Slot& s = d.slots[b % d.slots.size()];
+                if ((rc = slot_begin(c, s))) return rc;
                 if ((rc = gather_rows(c, *A.ix, s, g0, g, L, g_last_len, prior, chunk))) return rc;
                 GhJob j = job;
                 j.data = s.d_buf;
@@ -479,7 +500,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
                 j.prior = prior;
                 j.n_msgs = g;
                 j.last_msg_len = g_last_len;
-                j.state = d.d_state;  // group-local [word][g]; launches are chained, so groups may share it
+                j.state = d.d_state;  // group-local [word][g]; kernels run in order on one stream, so groups may share it
                 if (j.sha1) j.sha1 += 20 * rel;
                 if (j.md5) j.md5 += 16 * rel;
                 if (j.sha256) j.sha256 += 32 * rel;
@@ -488,22 +509,13 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
                     j.ok_words = d.d_ok;
                     j.ok_base = rel;
                 }
-                if (have_chain) GH_CUDA(c, cudaStreamWaitEvent(s.stream, d.chain, 0));
-                if ((rc = launch_window(c, d, A.algos, j, s.stream, true))) return rc;
-                GH_CUDA(c, cudaEventRecord(d.chain, s.stream));
-                have_chain = true;
+                if ((rc = slot_launch(c, d, s, A.algos, j))) return rc;
             }
         }
     }
     const size_t last_timing_event = d.ev_used;
 
-    // results back: wait for every slot stream, then one D2H per selected output
-    for (auto& s : d.slots) {
-        EvPair ev;
-        if ((rc = next_events(c, d, &ev))) return rc;
-        GH_CUDA(c, cudaEventRecord(ev.a, s.stream));
-        GH_CUDA(c, cudaStreamWaitEvent(d.stream, ev.a, 0));
-    }
+    // results back: every kernel ran on d.stream, so the D2H copies simply follow them there
     struct { int alg; uint64_t off; int idx; } outs[3] = {{GH_SHA1, o_sha1, 0}, {GH_MD5, o_md5, 1}, {GH_SHA256, o_sha256, 2}};
     for (auto& o : outs) {
         if (!(A.algos & o.alg) || !A.out[o.idx]) continue;
@@ -658,6 +670,7 @@ int gh_create(gh_ctx** out, const gh_config* cfg) {
             ok = ok && cudaMalloc(reinterpret_cast<void**>(&s.d_buf), c->slot_bytes + 256) == cudaSuccess;
             ok = ok && cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) == cudaSuccess;
             ok = ok && cudaEventCreateWithFlags(&s.h2d_done, cudaEventDisableTiming) == cudaSuccess;
+            ok = ok && cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming) == cudaSuccess;
         }
         if (!ok) {
             cudaError_t le = cudaGetLastError();
@@ -680,13 +693,13 @@ void gh_destroy(gh_ctx* c) {
             if (s.h_pin) cudaFreeHost(s.h_pin);
             if (s.stream) cudaStreamDestroy(s.stream);
             if (s.h2d_done) cudaEventDestroy(s.h2d_done);
+            if (s.consumed) cudaEventDestroy(s.consumed);
         }
         if (d.d_out) cudaFree(d.d_out);
         if (d.d_ok) cudaFree(d.d_ok);
         if (d.d_state) cudaFree(d.d_state);
         if (d.h_out) cudaFreeHost(d.h_out);
         for (auto e : d.ev_pool) cudaEventDestroy(e);
-        if (d.chain) cudaEventDestroy(d.chain);
         if (d.stream) cudaStreamDestroy(d.stream);
     }
     delete c->pool;

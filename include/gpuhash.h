@@ -53,7 +53,7 @@ typedef struct {
     int        n_devices;     /* 0 = every visible device */
     const int* devices;       /* CUDA ordinals, NULL = 0..n_devices-1 */
     uint64_t   slot_bytes;    /* device bytes per ring slot, 0 = default (256 MiB) */
-    int        slots;         /* ring slots per device, 0 = default (3), minimum 2 */
+    int        slots;         /* ring slots per device, 0 = default (4), minimum 2 */
     int        stage_threads; /* host threads copying pageable spans into the pinned ring, 0 = default (4) */
 } gh_config;
 

@@ -352,3 +352,31 @@ def test_lane_kernels_with_role_split_disabled():
                         "differential or chunk_interleaved or resumable or cfg5 or padding or cfg3"],
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_multi_device_context_shards_pieces():
+    """In-process multi-GPU: one context over every visible device, pieces sharded in contiguous
+    64-aligned ranges, bitmap words and digests merged on the host. Needs >= 2 GPUs."""
+    torch = _torch()
+    if torch.cuda.device_count() < 2:
+        pytest.skip("single-GPU box")
+    ctx = gpuhash.Context()  # all devices
+    try:
+        assert ctx.n_devices == torch.cuda.device_count()
+        L = 16384
+        total = 1000 * L + 4097
+        data = oracle.gen(8, 0, total)
+        expected = oracle.hash_msgs(oracle.SHA1, data, L, 4)
+        dirty = data.copy()
+        bad = [0, 63, 64, 65, 500, 1000]
+        for i in bad:
+            dirty[i * L + 7] ^= 0x80
+        bitmap, dig, nbad = ctx.VerifyPieces([dirty], L, expected)
+        want_bitmap, want_bad = oracle.verify_pieces(dirty, L, expected, 4)
+        assert nbad == want_bad == len(bad) and np.array_equal(bitmap, want_bitmap)
+        assert np.array_equal(dig, oracle.hash_msgs(oracle.SHA1, dirty, L, 4))
+        parts = ctx.HashParts([data], 1 << 20, gpuhash.MD5 | gpuhash.SHA256)
+        assert np.array_equal(parts[gpuhash.MD5], oracle.hash_msgs(oracle.MD5, data, 1 << 20, 4))
+        assert np.array_equal(parts[gpuhash.SHA256], oracle.hash_msgs(oracle.SHA256, data, 1 << 20, 4))
+    finally:
+        ctx.close()
