@@ -10,6 +10,8 @@
 // thread pool. Pieces / parts are independent, so devices get contiguous 64-aligned message ranges and
 // there is no collective of any kind.
 #include <cuda_runtime.h>
+#include <fcntl.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <atomic>
@@ -75,6 +77,69 @@ class Pool {
         }
         std::unique_lock<std::mutex> lk(dmu);
         dcv.wait(lk, [&] { return pending.load() == 0; });
+    }
+
+    // fn(i) for i in [0, n), spread over the pool; returns when all are done.
+    void parallel_for(uint64_t n, const std::function<void(uint64_t)>& fn) {
+        if (n == 0) return;
+        if (threads_.empty() || n == 1) {
+            for (uint64_t i = 0; i < n; i++) fn(i);
+            return;
+        }
+        std::atomic<uint64_t> next{0};
+        std::atomic<int> pending{0};
+        std::mutex dmu;
+        std::condition_variable dcv;
+        const int workers = static_cast<int>(std::min<uint64_t>(n, threads_.size()));
+        pending = workers;
+        for (int w = 0; w < workers; w++) {
+            std::lock_guard<std::mutex> g(mu_);
+            q_.push_back([&] {
+                for (;;) {
+                    const uint64_t i = next.fetch_add(1);
+                    if (i >= n) break;
+                    fn(i);
+                }
+                if (pending.fetch_sub(1) == 1) {
+                    std::lock_guard<std::mutex> g2(dmu);
+                    dcv.notify_one();
+                }
+            });
+            cv_.notify_one();
+        }
+        std::unique_lock<std::mutex> lk(dmu);
+        dcv.wait(lk, [&] { return pending.load() == 0; });
+    }
+    // pread of [off, off+n) into dst, in 4 MiB pieces over the pool; bytes the file does not have
+    // (missing or short file) read as zeros, so the pieces that touch them simply fail verification.
+    void read(int fd, uint64_t off, uint8_t* dst, uint64_t n) {
+        const uint64_t grain = 4ull << 20;
+        parallel_for((n + grain - 1) / grain, [&](uint64_t i) {
+            uint64_t o = i * grain, len = std::min(grain, n - o);
+            uint8_t* p = dst + o;
+            while (len) {
+                const ssize_t r = fd >= 0 ? pread(fd, p, len, static_cast<off_t>(off + o)) : 0;
+                if (r <= 0) {
+                    memset(p, 0, len);
+                    break;
+                }
+                p += r; o += r; len -= r;
+            }
+        });
+    }
+    void read2d(int fd, uint64_t off, uint64_t spitch, uint8_t* dst, uint64_t dpitch, uint64_t width, uint64_t rows) {
+        parallel_for(rows, [&](uint64_t r) {
+            uint64_t o = off + r * spitch, len = width;
+            uint8_t* p = dst + r * dpitch;
+            while (len) {
+                const ssize_t k = fd >= 0 ? pread(fd, p, len, static_cast<off_t>(o)) : 0;
+                if (k <= 0) {
+                    memset(p, 0, len);
+                    break;
+                }
+                p += k; o += k; len -= k;
+            }
+        });
     }
 
     // strided copy: rows of `width` bytes, pitches in bytes; rows are spread over the pool.
@@ -257,29 +322,55 @@ int launch_window(gh_ctx* c, Device& d, int algos, GhJob job, cudaStream_t strea
 }
 
 // --------------------------------------------------------------------------- span gather
+// The logical stream as a list of runs: each run is host memory (ptr) or a byte range of a file (fd).
 struct SpanIndex {
-    const gh_span* spans;
-    size_t n;
-    std::vector<uint64_t> start;  // stream offset of each span, plus the total at [n]
+    size_t n = 0;
+    std::vector<const uint8_t*> ptr;  // null for file-backed runs
+    std::vector<int> fd;              // -1 for memory runs and for files that could not be opened
+    std::vector<char> is_file;
+    std::vector<uint64_t> start;      // stream offset of each run, plus the total at [n]
     std::vector<char> pinned;
     uint64_t total() const { return start[n]; }
+    ~SpanIndex() {
+        for (size_t i = 0; i < fd.size(); i++)
+            if (fd[i] >= 0) close(fd[i]);
+    }
 };
 
 void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
-    ix->spans = spans;
     ix->n = n;
+    ix->ptr.resize(n);
+    ix->fd.assign(n, -1);
+    ix->is_file.assign(n, 0);
     ix->start.resize(n + 1);
     ix->pinned.resize(n);
     uint64_t off = 0;
     for (size_t i = 0; i < n; i++) {
         ix->start[i] = off;
         off += spans[i].len;
+        ix->ptr[i] = static_cast<const uint8_t*>(spans[i].host_ptr);
         cudaPointerAttributes a{};
         bool pinned = false;
         if (spans[i].len && cudaPointerGetAttributes(&a, spans[i].host_ptr) == cudaSuccess)
             pinned = a.type == cudaMemoryTypeHost;
         cudaGetLastError();  // older drivers flag unregistered memory as an error; clear it
         ix->pinned[i] = pinned;
+    }
+    ix->start[n] = off;
+}
+
+void build_index_files(const gh_file* files, size_t n, SpanIndex* ix) {
+    ix->n = n;
+    ix->ptr.assign(n, nullptr);
+    ix->fd.assign(n, -1);
+    ix->is_file.assign(n, 1);
+    ix->start.resize(n + 1);
+    ix->pinned.assign(n, 0);
+    uint64_t off = 0;
+    for (size_t i = 0; i < n; i++) {
+        ix->start[i] = off;
+        off += files[i].len;
+        if (files[i].len && files[i].path) ix->fd[i] = open(files[i].path, O_RDONLY | O_CLOEXEC);
     }
     ix->start[n] = off;
 }
@@ -296,7 +387,7 @@ int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint
         const uint64_t s_lo = ix.start[i], s_hi = ix.start[i + 1];
         if (s_hi <= x) { i++; continue; }
         const uint64_t hi = std::min(b, s_hi);
-        const uint8_t* src = static_cast<const uint8_t*>(ix.spans[i].host_ptr) + (x - s_lo);
+        const uint8_t* src = ix.ptr[i] + (x - s_lo);
         const uint64_t len = hi - x;
         const uint64_t doff = dst_off + (x - a);
         if (ix.pinned[i]) {
@@ -307,7 +398,8 @@ int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint
                 GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
                 s.h2d_pending = false;
             }
-            c->pool->copy(s.h_pin + doff, src, len);
+            if (ix.is_file[i]) c->pool->read(ix.fd[i], x - s_lo, s.h_pin + doff, len);
+            else c->pool->copy(s.h_pin + doff, src, len);
             *staged_lo = std::min(*staged_lo, doff);
             *staged_hi = std::max(*staged_hi, doff + len);
         }
@@ -366,7 +458,7 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g
             if ((g0 + m2) * L + prior + w > ix.start[si + 1]) break;
             rows++;
         }
-        const uint8_t* src = static_cast<const uint8_t*>(ix.spans[si].host_ptr) + (lo - ix.start[si]);
+        const uint8_t* src = ix.ptr[si] + (lo - ix.start[si]);
         if (ix.pinned[si]) {
             static const bool no2d = getenv("GPUHASH_NO_2D") != nullptr;
             if (no2d) {
@@ -381,7 +473,8 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g
                 GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
                 s.h2d_pending = false;
             }
-            c->pool->copy2d(s.h_pin + m * chunk, chunk, src, L, w, rows);
+            if (ix.is_file[si]) c->pool->read2d(ix.fd[si], lo - ix.start[si], L, s.h_pin + m * chunk, chunk, w, rows);
+            else c->pool->copy2d(s.h_pin + m * chunk, chunk, src, L, w, rows);
             st_lo = std::min(st_lo, m * chunk);
             st_hi = std::max(st_hi, (m + rows - 1) * chunk + w);
         }
@@ -548,20 +641,41 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
     return GH_OK;
 }
 
+int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8_t* expected, uint8_t* sha1_out,
+              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad);
+
 int run_batch(gh_ctx* c, const gh_span* spans, size_t n_spans, uint64_t msg_len, int algos, const uint8_t* expected,
               uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
     if (!c) return GH_EINVAL;
     std::lock_guard<std::mutex> g(c->mu);
-    if (c->lost) return fail(c, GH_ECTX_LOST, "context lost after a device fault");
-    if (msg_len == 0) return fail(c, GH_EINVAL, "message length must be > 0");
     if (n_spans && !spans) return fail(c, GH_EINVAL, "spans is NULL");
-    if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256)))
-        return fail(c, GH_EINVAL, "algos must be a mask of GH_SHA1|GH_MD5|GH_SHA256");
     for (size_t i = 0; i < n_spans; i++)
         if (spans[i].len && !spans[i].host_ptr) return fail(c, GH_EINVAL, "span with NULL pointer and non-zero length");
-    const auto t0 = std::chrono::steady_clock::now();
     SpanIndex ix;
     build_index(spans, n_spans, &ix);
+    return run_index(c, ix, msg_len, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad);
+}
+
+int run_files(gh_ctx* c, const gh_file* files, size_t n_files, uint64_t msg_len, int algos, const uint8_t* expected,
+              uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+    if (!c) return GH_EINVAL;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (n_files && !files) return fail(c, GH_EINVAL, "files is NULL");
+    for (size_t i = 0; i < n_files; i++)
+        if (files[i].len && !files[i].path) return fail(c, GH_EINVAL, "file with NULL path and non-zero length");
+    SpanIndex ix;
+    build_index_files(files, n_files, &ix);
+    return run_index(c, ix, msg_len, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad);
+}
+
+// caller holds c->mu
+int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8_t* expected, uint8_t* sha1_out,
+              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+    if (c->lost) return fail(c, GH_ECTX_LOST, "context lost after a device fault");
+    if (msg_len == 0) return fail(c, GH_EINVAL, "message length must be > 0");
+    if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256)))
+        return fail(c, GH_EINVAL, "algos must be a mask of GH_SHA1|GH_MD5|GH_SHA256");
+    const auto t0 = std::chrono::steady_clock::now();
     const uint64_t n = count_msgs(ix.total(), msg_len);
     if (n_bad) *n_bad = 0;
     if (n == 0) {
@@ -726,6 +840,17 @@ int gh_verify_pieces(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t
 int gh_hash_parts(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t part_len, int algos, uint8_t* sha1_out,
                   uint8_t* md5_out, uint8_t* sha256_out) {
     return run_batch(ctx, spans, n_spans, part_len, algos, nullptr, sha1_out, md5_out, sha256_out, nullptr, nullptr);
+}
+
+int gh_verify_files(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t piece_len, const uint8_t* expected,
+                    uint8_t* digests_out, uint64_t* ok_bitmap_out, uint64_t* n_bad_out) {
+    return run_files(ctx, files, n_files, piece_len, GH_SHA1, expected, digests_out, nullptr, nullptr, ok_bitmap_out,
+                     n_bad_out);
+}
+
+int gh_hash_file_parts(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t part_len, int algos,
+                       uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out) {
+    return run_files(ctx, files, n_files, part_len, algos, nullptr, sha1_out, md5_out, sha256_out, nullptr, nullptr);
 }
 
 int gh_s3_etag(gh_ctx* ctx, const uint8_t* part_md5s, uint64_t n_parts, char* out, size_t out_len) {

@@ -42,6 +42,10 @@ class Config(ctypes.Structure):
                 ("slot_bytes", ctypes.c_uint64), ("slots", ctypes.c_int), ("stage_threads", ctypes.c_int)]
 
 
+class File(ctypes.Structure):
+    _fields_ = [("path", ctypes.c_char_p), ("len", ctypes.c_uint64)]
+
+
 class Stats(ctypes.Structure):
     _fields_ = [("kernel_launches", ctypes.c_uint64), ("h2d_bytes", ctypes.c_uint64),
                 ("d2h_bytes", ctypes.c_uint64), ("kernel_ms", ctypes.c_double), ("wall_ms", ctypes.c_double)]
@@ -62,6 +66,19 @@ ABI = {
     "gh_verify_pieces": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_hash_parts": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _INT, _VP, _VP, _VP]),
     "gh_s3_etag": (_INT, [_VP, _VP, _U64, ctypes.c_char_p, _SZ]),
+    "gh_verify_files": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
+    "gh_hash_file_parts": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _INT, _VP, _VP, _VP]),
+    "gh_metainfo_parse": (_INT, [_VP, _SZ, ctypes.POINTER(_VP), ctypes.c_char_p, _SZ]),
+    "gh_metainfo_free": (None, [_VP]),
+    "gh_metainfo_piece_length": (_U64, [_VP]),
+    "gh_metainfo_n_pieces": (_U64, [_VP]),
+    "gh_metainfo_total_length": (_U64, [_VP]),
+    "gh_metainfo_pieces": (_VP, [_VP]),
+    "gh_metainfo_name": (ctypes.c_char_p, [_VP]),
+    "gh_metainfo_n_files": (_SZ, [_VP]),
+    "gh_metainfo_file": (_INT, [_VP, _SZ, ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(_U64)]),
+    "gh_metainfo_info_hash": (_INT, [_VP, _VP, _VP]),
+    "gh_verify_torrent": (_INT, [_VP, _VP, ctypes.c_char_p, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_verify_pieces_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _VP, _VP, _VP, _VP]),
     "gh_hash_parts_device": (_INT, [_VP, _INT, _VP, _U64, _U64, _INT, _VP, _VP, _VP, _VP]),
     "gh_hash_update_device": (_INT, [_VP, _INT, _INT, _VP, _U64, _U64, _U64, _U64, _U64, _U64, _VP, _VP, _VP, _VP, _VP]),
@@ -138,6 +155,38 @@ def _u8(a):
 
 def _ptr(a):
     return ctypes.c_void_p(a.ctypes.data) if a is not None and a.size else None
+
+
+class Metainfo:
+    """Parsed BEP 3 metainfo (gh_metainfo_*): a .torrent file's bytes or a bare info dictionary."""
+
+    def __init__(self, data):
+        L = load()
+        a = _u8(data)
+        h = ctypes.c_void_p()
+        err = ctypes.create_string_buffer(256)
+        rc = L.gh_metainfo_parse(_ptr(a), a.size, ctypes.byref(h), err, 256)
+        if rc:
+            raise GpuHashError(rc, "gh_metainfo_parse", err.value.decode())
+        self.h, self.L = h, L
+        self.piece_length = int(L.gh_metainfo_piece_length(h))
+        self.n_pieces = int(L.gh_metainfo_n_pieces(h))
+        self.total_length = int(L.gh_metainfo_total_length(h))
+        self.name = L.gh_metainfo_name(h).decode()
+        self.pieces = ctypes.string_at(L.gh_metainfo_pieces(h), 20 * self.n_pieces) if self.n_pieces else b""
+        self.files = []
+        for i in range(L.gh_metainfo_n_files(h)):
+            p, n = ctypes.c_char_p(), ctypes.c_uint64()
+            L.gh_metainfo_file(h, i, ctypes.byref(p), ctypes.byref(n))
+            self.files.append((p.value.decode(), int(n.value)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.gh_metainfo_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
 
 
 class PinnedBuffer:
@@ -237,6 +286,55 @@ class Context:
                                   _ptr(outs.get(SHA256)))
         self._check(rc, "gh_hash_parts")
         return outs
+
+    @staticmethod
+    def _files(files):
+        arr = (File * max(len(files), 1))()
+        keep = []
+        total = 0
+        for i, (path, n) in enumerate(files):
+            b = os.fsencode(path)
+            keep.append(b)
+            arr[i].path, arr[i].len = b, n
+            total += n
+        return arr, keep, total
+
+    def VerifyFiles(self, files, piece_len, expected=None):
+        """files: [(path, length)] in info order; the library reads them itself."""
+        arr, keep, total = self._files(files)
+        n = count(total, piece_len) if piece_len > 0 else 0
+        exp = _u8(expected) if expected is not None else None
+        dig = np.zeros((n, 20), dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        nbad = ctypes.c_uint64()
+        rc = self.L.gh_verify_files(self.h, arr, len(files), piece_len, _ptr(exp), _ptr(dig), _ptr(bitmap),
+                                    ctypes.byref(nbad))
+        self._check(rc, "gh_verify_files")
+        return bitmap, dig, int(nbad.value)
+
+    def HashFileParts(self, files, part_len, algos):
+        arr, keep, total = self._files(files)
+        n = count(total, part_len) if part_len > 0 else 0
+        outs = {a: np.zeros((n, DIGEST_LEN[a]), dtype=np.uint8) for a in (SHA1, MD5, SHA256) if algos & a}
+        rc = self.L.gh_hash_file_parts(self.h, arr, len(files), part_len, algos, _ptr(outs.get(SHA1)),
+                                       _ptr(outs.get(MD5)), _ptr(outs.get(SHA256)))
+        self._check(rc, "gh_hash_file_parts")
+        return outs
+
+    def InfoHash(self, metainfo):
+        out = np.zeros(20, dtype=np.uint8)
+        self._check(self.L.gh_metainfo_info_hash(self.h, metainfo.h, _ptr(out)), "gh_metainfo_info_hash")
+        return out.tobytes()
+
+    def VerifyTorrent(self, metainfo, base_dir):
+        n = metainfo.n_pieces
+        dig = np.zeros((n, 20), dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        nbad = ctypes.c_uint64()
+        rc = self.L.gh_verify_torrent(self.h, metainfo.h, os.fsencode(base_dir), _ptr(dig), _ptr(bitmap),
+                                      ctypes.byref(nbad))
+        self._check(rc, "gh_verify_torrent")
+        return bitmap, dig, int(nbad.value)
 
     def S3ETag(self, part_md5s):
         a = _u8(part_md5s)

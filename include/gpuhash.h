@@ -104,6 +104,48 @@ int gh_verify_pieces(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t
 int gh_hash_parts(gh_ctx* ctx, const gh_span* spans, size_t n_spans, uint64_t part_len, int algos,
                   uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out);
 
+/* The same two calls for payload that lives in FILES: the library preads the files into its pinned
+ * ring itself (in parallel, page-cache reads), so no payload byte crosses the FFI or needs a
+ * caller-side buffer. This is the shape of both reference call sites: anacrolix's file storage under
+ * baseDir (torrent.go:41) read back by hashPiece, and the *os.File handed to PutObjectWithContext
+ * (uploader.go:73-89). `len` is the length the metainfo / stat promises; a file that is missing or
+ * shorter reads as zeros from there on, so exactly the pieces that touch the hole fail. */
+typedef struct {
+    const char* path;
+    uint64_t    len;
+} gh_file;
+int gh_verify_files(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t piece_len,
+                    const uint8_t* expected, uint8_t* digests_out, uint64_t* ok_bitmap_out,
+                    uint64_t* n_bad_out);
+int gh_hash_file_parts(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t part_len, int algos,
+                       uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out);
+
+/* ---- metainfo (BEP 3 .torrent / info dictionary) ------------------------------------------------- */
+/* The data format on the input side of piece verification. In the reference the info dictionary
+ * arrives after client.AddMagnet (torrent.go:58) and is awaited at torrent.go:69 (<-t.GotInfo());
+ * anacrolix's metainfo package turns it into piece length, piece hashes and the file list that the
+ * file storage of torrent.go:41 lays out under baseDir. gh_metainfo_parse accepts a whole .torrent
+ * (top-level dictionary with "info") or a bare info dictionary; paths with "..", empty or absolute
+ * components are rejected. Host-only: needs no device. err (optional) receives a reason. */
+typedef struct gh_metainfo gh_metainfo;
+int            gh_metainfo_parse(const uint8_t* data, size_t len, gh_metainfo** out, char* err, size_t err_len);
+void           gh_metainfo_free(gh_metainfo* m);
+uint64_t       gh_metainfo_piece_length(const gh_metainfo* m);
+uint64_t       gh_metainfo_n_pieces(const gh_metainfo* m);
+uint64_t       gh_metainfo_total_length(const gh_metainfo* m);
+const uint8_t* gh_metainfo_pieces(const gh_metainfo* m);      /* 20 * n_pieces bytes, owned by m */
+const char*    gh_metainfo_name(const gh_metainfo* m);
+size_t         gh_metainfo_n_files(const gh_metainfo* m);
+/* file i in info order; rel_path is relative to the storage base dir (name/, then the path list, for
+ * multi-file torrents; name for single-file ones -- anacrolix file storage's layout) */
+int            gh_metainfo_file(const gh_metainfo* m, size_t i, const char** rel_path, uint64_t* len);
+/* info-hash = SHA-1 of the bencoded info dictionary (the magnet link's btih), computed on the device */
+int            gh_metainfo_info_hash(gh_ctx* ctx, const gh_metainfo* m, uint8_t out[20]);
+/* Verify a downloaded torrent in place: files under base_dir as laid out above, expected hashes
+ * from the metainfo. The batched form of what runs between torrent.go:79 and :106. */
+int            gh_verify_torrent(gh_ctx* ctx, const gh_metainfo* m, const char* base_dir,
+                                 uint8_t* digests_out, uint64_t* ok_bitmap_out, uint64_t* n_bad_out);
+
 /* S3 multipart ETag of n binary part MD5s: hex(md5(concat)) + "-" + n (what the server returns for
  * the upload started at uploader.go:89; computed on the device like any other message).
  * out needs at least 56 bytes. */
