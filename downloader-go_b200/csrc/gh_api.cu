@@ -227,6 +227,7 @@ struct gh_ctx {
     gh_stats stats{};
     std::atomic<uint64_t> launches{0}, h2d{0}, d2h{0};
     bool lost = false;
+    bool stream_open = false;  // a gh_stream owns the ring until it is finished or aborted
 };
 
 namespace {
@@ -672,6 +673,7 @@ int run_files(gh_ctx* c, const gh_file* files, size_t n_files, uint64_t msg_len,
 int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8_t* expected, uint8_t* sha1_out,
               uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
     if (c->lost) return fail(c, GH_ECTX_LOST, "context lost after a device fault");
+    if (c->stream_open) return fail(c, GH_EINVAL, "a gh_stream is open on this context; finish or abort it first");
     if (msg_len == 0) return fail(c, GH_EINVAL, "message length must be > 0");
     if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256)))
         return fail(c, GH_EINVAL, "algos must be a mask of GH_SHA1|GH_MD5|GH_SHA256");
@@ -867,6 +869,204 @@ int gh_s3_etag(gh_ctx* ctx, const uint8_t* part_md5s, uint64_t n_parts, char* ou
     for (int i = 0; i < 16; i++) snprintf(out + 2 * i, 3, "%02x", d[i]);
     snprintf(out + 32, out_len - 32, "-%llu", static_cast<unsigned long long>(n_parts));
     return GH_OK;
+}
+
+// ---- incremental feed ----------------------------------------------------------------------
+struct gh_stream {
+    gh_ctx* c = nullptr;
+    int algos = 0;
+    uint64_t L = 0, total = 0, n = 0, per = 0;
+    uint64_t next_msg = 0, window = 0, fed = 0;
+    bool want_ok = false, acquired = false;
+    uint64_t o_sha1 = 0, o_md5 = 0, o_sha256 = 0, o_exp = 0, ok_words = 0;
+    uint64_t cap = 0;  // bytes the acquired window must receive
+};
+
+static void stream_release(gh_stream* st) {
+    if (!st) return;
+    {
+        std::lock_guard<std::mutex> g(st->c->mu);
+        st->c->stream_open = false;
+    }
+    delete st;
+}
+
+int gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len, const uint8_t* expected,
+                   gh_stream** out) {
+    if (!ctx || !out) return GH_EINVAL;
+    *out = nullptr;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    if (ctx->lost) return GH_ECTX_LOST;
+    if (ctx->stream_open) return fail(ctx, GH_EINVAL, "a gh_stream is already open on this context");
+    if (msg_len == 0) return fail(ctx, GH_EINVAL, "message length must be > 0");
+    if (!(algos & 7) || (algos & ~7)) return fail(ctx, GH_EINVAL, "bad algos mask");
+    if (msg_len > ctx->slot_bytes)
+        return fail(ctx, GH_ERANGE, "message longer than a ring slot: use gh_hash_parts / gh_hash_file_parts, which interleave");
+    Device& d = ctx->devs[0];
+    GH_CUDA(ctx, cudaSetDevice(d.ordinal));
+    gh_stream* st = new gh_stream();
+    st->c = ctx;
+    st->algos = algos;
+    st->L = msg_len;
+    st->total = total_len;
+    st->n = count_msgs(total_len, msg_len);
+    st->per = std::max<uint64_t>(1, ctx->slot_bytes / msg_len);
+    st->want_ok = expected != nullptr && (algos & GH_SHA1);
+    auto al = [](uint64_t v) { return (v + 255) & ~255ull; };
+    const uint64_t n = std::max<uint64_t>(st->n, 1);
+    st->o_sha1 = 0;
+    st->o_md5 = al(20 * n);
+    st->o_sha256 = st->o_md5 + al(16 * n);
+    st->o_exp = st->o_sha256 + al(32 * n);
+    st->ok_words = (n + 31) / 32;
+    const uint64_t out_bytes = st->o_exp + al(20 * n);
+    int rc;
+    if ((rc = grow(ctx, &d.d_out, &d.d_out_cap, out_bytes)) || (rc = grow(ctx, &d.h_out, &d.h_out_cap, out_bytes, true)) ||
+        (rc = grow(ctx, &d.d_ok, &d.d_ok_cap, (st->ok_words + 1) * 4))) {
+        delete st;
+        return rc;
+    }
+    if (st->want_ok) {
+        memcpy(d.h_out + st->o_exp, expected, 20 * st->n);
+        cudaError_t e = cudaMemcpyAsync(d.d_out + st->o_exp, d.h_out + st->o_exp, 20 * st->n, cudaMemcpyHostToDevice, d.stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(d.d_ok, 0, (st->ok_words + 1) * 4, d.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);  // h_out is reused for results later
+        if (e != cudaSuccess) {
+            delete st;
+            return cuda_fail(ctx, e, "gh_stream_open");
+        }
+    }
+    for (auto& sl : d.slots) sl.in_use = false;
+    d.ev_used = 0;
+    ctx->stream_open = true;
+    *out = st;
+    return GH_OK;
+}
+
+int gh_stream_acquire(gh_stream* st, void** buf, uint64_t* cap) {
+    if (!st || !buf || !cap) return GH_EINVAL;
+    gh_ctx* c = st->c;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (st->acquired) return fail(c, GH_EINVAL, "gh_stream_acquire: the previous window was not submitted");
+    if (st->next_msg >= st->n) {
+        *buf = nullptr;
+        *cap = 0;
+        return GH_OK;  // everything has been fed
+    }
+    Device& d = c->devs[0];
+    GH_CUDA(c, cudaSetDevice(d.ordinal));
+    Slot& s = d.slots[st->window % d.slots.size()];
+    if (!s.h_pin) GH_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256));
+    if (s.h2d_pending) {  // the DMA that last read this pinned buffer must have drained
+        GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
+        s.h2d_pending = false;
+    }
+    const uint64_t k = std::min(st->per, st->n - st->next_msg);
+    const uint64_t lo = st->next_msg * st->L, hi = std::min((st->next_msg + k) * st->L, st->total);
+    st->cap = hi - lo;
+    st->acquired = true;
+    *buf = s.h_pin;
+    *cap = st->cap;
+    return GH_OK;
+}
+
+int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
+    if (!st) return GH_EINVAL;
+    gh_ctx* c = st->c;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (!st->acquired) return fail(c, GH_EINVAL, "gh_stream_submit without gh_stream_acquire");
+    if (n_bytes != st->cap) return fail(c, GH_EINVAL, "gh_stream_submit: a window must be filled completely (cap bytes)");
+    Device& d = c->devs[0];
+    GH_CUDA(c, cudaSetDevice(d.ordinal));
+    Slot& s = d.slots[st->window % d.slots.size()];
+    int rc;
+    if ((rc = slot_begin(c, s))) return rc;
+    if ((rc = flush_staged(c, s, 0, n_bytes))) return rc;
+    c->h2d += n_bytes;
+    const uint64_t k = std::min(st->per, st->n - st->next_msg);
+    GhJob j{};
+    j.data = s.d_buf;
+    j.stride = st->L;
+    j.chunk_len = st->L;
+    j.n_msgs = k;
+    j.msg_len = st->L;
+    j.last_msg_len = (st->next_msg + k == st->n) ? st->total - (st->n - 1) * st->L : st->L;
+    const uint64_t rel = st->next_msg;
+    if (st->algos & GH_SHA1) j.sha1 = d.d_out + st->o_sha1 + 20 * rel;
+    if (st->algos & GH_MD5) j.md5 = d.d_out + st->o_md5 + 16 * rel;
+    if (st->algos & GH_SHA256) j.sha256 = d.d_out + st->o_sha256 + 32 * rel;
+    if (st->want_ok) {
+        j.expected = d.d_out + st->o_exp + 20 * rel;
+        j.ok_words = d.d_ok;
+        j.ok_base = rel;
+    }
+    if ((rc = slot_launch(c, d, s, st->algos, j))) return rc;
+    st->next_msg += k;
+    st->fed += n_bytes;
+    st->window++;
+    st->acquired = false;
+    return GH_OK;
+}
+
+int gh_stream_finish(gh_stream* st, uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* ok_bitmap_out,
+                     uint64_t* n_bad_out) {
+    if (!st) return GH_EINVAL;
+    gh_ctx* c = st->c;
+    int rc = GH_OK;
+    {
+        std::lock_guard<std::mutex> g(c->mu);
+        Device& d = c->devs[0];
+        if (st->next_msg != st->n || st->acquired) {
+            rc = fail(c, GH_EINVAL, "gh_stream_finish before every window was submitted (use gh_stream_abort to give up)");
+        } else if (cudaSetDevice(d.ordinal) != cudaSuccess) {
+            rc = GH_ECUDA;
+        } else {
+            const uint64_t n = st->n;
+            cudaError_t e = cudaSuccess;
+            struct { int alg; uint64_t off; uint8_t* dst; int dl; } outs[3] = {
+                {GH_SHA1, st->o_sha1, sha1_out, 20}, {GH_MD5, st->o_md5, md5_out, 16}, {GH_SHA256, st->o_sha256, sha256_out, 32}};
+            for (auto& o : outs)
+                if ((st->algos & o.alg) && o.dst && n && e == cudaSuccess) {
+                    e = cudaMemcpyAsync(d.h_out + o.off, d.d_out + o.off, o.dl * n, cudaMemcpyDeviceToHost, d.stream);
+                    c->d2h += o.dl * n;
+                }
+            uint32_t* h_ok = reinterpret_cast<uint32_t*>(d.h_out + st->o_exp);
+            if (st->want_ok && n && e == cudaSuccess)
+                e = cudaMemcpyAsync(h_ok, d.d_ok, st->ok_words * 4, cudaMemcpyDeviceToHost, d.stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);
+            for (auto& sl : d.slots) sl.h2d_pending = false;
+            if (e != cudaSuccess) {
+                rc = cuda_fail(c, e, "gh_stream_finish");
+            } else {
+                for (auto& o : outs)
+                    if ((st->algos & o.alg) && o.dst && n) memcpy(o.dst, d.h_out + o.off, o.dl * n);
+                if (n_bad_out) *n_bad_out = 0;
+                if (ok_bitmap_out && n) {
+                    memset(ok_bitmap_out, 0, ((n + 63) / 64) * 8);
+                    if (st->want_ok) {
+                        memcpy(ok_bitmap_out, h_ok, st->ok_words * 4);
+                        uint64_t good = 0;
+                        for (uint64_t w = 0; w < (n + 63) / 64; w++) good += __builtin_popcountll(ok_bitmap_out[w]);
+                        if (n_bad_out) *n_bad_out = n - good;
+                    }
+                }
+            }
+        }
+    }
+    if (rc == GH_OK || rc == GH_ECUDA || rc == GH_ECTX_LOST) stream_release(st);
+    return rc;
+}
+
+void gh_stream_abort(gh_stream* st) {
+    if (!st) return;
+    gh_ctx* c = st->c;
+    {
+        std::lock_guard<std::mutex> g(c->mu);
+        Device& d = c->devs[0];
+        if (cudaSetDevice(d.ordinal) == cudaSuccess) cudaDeviceSynchronize();
+        for (auto& sl : d.slots) sl.h2d_pending = false;
+    }
+    stream_release(st);
 }
 
 // ---- device-resident -----------------------------------------------------------------------

@@ -68,6 +68,11 @@ ABI = {
     "gh_s3_etag": (_INT, [_VP, _VP, _U64, ctypes.c_char_p, _SZ]),
     "gh_verify_files": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_hash_file_parts": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _INT, _VP, _VP, _VP]),
+    "gh_stream_open": (_INT, [_VP, _INT, _U64, _U64, _VP, ctypes.POINTER(_VP)]),
+    "gh_stream_acquire": (_INT, [_VP, ctypes.POINTER(_VP), ctypes.POINTER(_U64)]),
+    "gh_stream_submit": (_INT, [_VP, _U64]),
+    "gh_stream_finish": (_INT, [_VP, _VP, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
+    "gh_stream_abort": (None, [_VP]),
     "gh_metainfo_parse": (_INT, [_VP, _SZ, ctypes.POINTER(_VP), ctypes.c_char_p, _SZ]),
     "gh_metainfo_free": (None, [_VP]),
     "gh_metainfo_piece_length": (_U64, [_VP]),
@@ -207,6 +212,55 @@ class PinnedBuffer:
             self.ptr = None
 
 
+class Stream:
+    """gh_stream_*: feed a payload window by window into the pinned ring.
+
+        st = ctx.Stream(gpuhash.SHA1, piece_len, total, expected)
+        while True:
+            buf = st.acquire()            # numpy uint8 view of the pinned window, or None when done
+            if buf is None: break
+            buf[:] = ...                  # exactly len(buf) bytes
+            st.submit()
+        bitmap, digests, n_bad = st.finish()
+    """
+
+    def __init__(self, ctx, algos, msg_len, total_len, expected=None):
+        self.ctx, self.algos, self.n = ctx, algos, count(total_len, msg_len) if msg_len > 0 else 0
+        self._exp = _u8(expected) if expected is not None else None
+        h = ctypes.c_void_p()
+        rc = ctx.L.gh_stream_open(ctx.h, algos, msg_len, total_len, _ptr(self._exp), ctypes.byref(h))
+        ctx._check(rc, "gh_stream_open")
+        self.h, self._cap = h, 0
+
+    def acquire(self):
+        buf, cap = ctypes.c_void_p(), ctypes.c_uint64()
+        self.ctx._check(self.ctx.L.gh_stream_acquire(self.h, ctypes.byref(buf), ctypes.byref(cap)), "gh_stream_acquire")
+        if not cap.value:
+            return None
+        self._cap = int(cap.value)
+        return np.ctypeslib.as_array((ctypes.c_uint8 * self._cap).from_address(buf.value))
+
+    def submit(self, n_bytes=None):
+        self.ctx._check(self.ctx.L.gh_stream_submit(self.h, self._cap if n_bytes is None else n_bytes), "gh_stream_submit")
+
+    def finish(self):
+        n = self.n
+        outs = {a: np.zeros((n, DIGEST_LEN[a]), dtype=np.uint8) for a in (SHA1, MD5, SHA256) if self.algos & a}
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        nbad = ctypes.c_uint64()
+        rc = self.ctx.L.gh_stream_finish(self.h, _ptr(outs.get(SHA1)), _ptr(outs.get(MD5)), _ptr(outs.get(SHA256)),
+                                         _ptr(bitmap), ctypes.byref(nbad))
+        if rc == GH_OK:
+            self.h = None
+        self.ctx._check(rc, "gh_stream_finish")
+        return bitmap, outs, int(nbad.value)
+
+    def abort(self):
+        if self.h:
+            self.ctx.L.gh_stream_abort(self.h)
+            self.h = None
+
+
 class Context:
     """One gh_ctx. `devices` is a list of CUDA ordinals (None = all visible)."""
 
@@ -335,6 +389,9 @@ class Context:
                                       ctypes.byref(nbad))
         self._check(rc, "gh_verify_torrent")
         return bitmap, dig, int(nbad.value)
+
+    def Stream(self, algos, msg_len, total_len, expected=None):
+        return Stream(self, algos, msg_len, total_len, expected)
 
     def S3ETag(self, part_md5s):
         a = _u8(part_md5s)

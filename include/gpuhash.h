@@ -120,6 +120,31 @@ int gh_verify_files(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t 
 int gh_hash_file_parts(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t part_len, int algos,
                        uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out);
 
+/* ---- incremental feed ------------------------------------------------------------------------- */
+/* For payload that arrives a window at a time (pieces as the swarm completes them, an HTTP body):
+ * the caller fills the library's pinned ring buffers in place, so the bytes are written once and
+ * DMA'd from where they landed. This is the micro-batching seam for anacrolix's per-piece hashPiece
+ * calls (torrent.go:79-106): flush every `cap` bytes instead of hashing piece by piece.
+ *   open    -> fixes algos, message length, total length and (optionally) the expected SHA-1s
+ *   acquire -> a pinned buffer and the number of bytes it must receive: whole messages, as many as
+ *              fit a ring slot (the last window holds the remainder). buf == NULL, cap == 0 when
+ *              everything has been fed. Blocks while the ring is full.
+ *   submit  -> the buffer holds exactly `cap` bytes: queue its DMA and kernel, return at once
+ *   finish  -> wait, return digests / bitmap / n_bad (same meaning as gh_verify_pieces), close
+ *   abort   -> drop the stream
+ * Messages longer than a ring slot are refused with GH_ERANGE (sequential feeding would leave one
+ * chain per window; gh_hash_parts / gh_hash_file_parts interleave such messages instead). A context
+ * carries one stream at a time and refuses one-shot calls while it is open. Uses the context's
+ * first device. */
+typedef struct gh_stream gh_stream;
+int  gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len, const uint8_t* expected,
+                    gh_stream** out);
+int  gh_stream_acquire(gh_stream* st, void** buf, uint64_t* cap);
+int  gh_stream_submit(gh_stream* st, uint64_t n_bytes);
+int  gh_stream_finish(gh_stream* st, uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out,
+                      uint64_t* ok_bitmap_out, uint64_t* n_bad_out);
+void gh_stream_abort(gh_stream* st);
+
 /* ---- metainfo (BEP 3 .torrent / info dictionary) ------------------------------------------------- */
 /* The data format on the input side of piece verification. In the reference the info dictionary
  * arrives after client.AddMagnet (torrent.go:58) and is awaited at torrent.go:69 (<-t.GotInfo());

@@ -380,3 +380,48 @@ def test_multi_device_context_shards_pieces():
         assert np.array_equal(parts[gpuhash.SHA256], oracle.hash_msgs(oracle.SHA256, data, 1 << 20, 4))
     finally:
         ctx.close()
+
+
+def test_incremental_stream_feed():
+    """gh_stream_*: windows of whole pieces written in place into the pinned ring, more windows than
+    slots, short last piece, one corrupted piece; and the refusals the header promises."""
+    ctx = gpuhash.Context(devices=[0], slot_bytes=1 << 20, slots=3)
+    try:
+        L = 16384
+        total = 500 * L + 999  # 501 pieces, 64 per window -> 8 windows on 3 slots
+        data = oracle.gen(6, 0, total)
+        expected = oracle.hash_msgs(oracle.SHA1, data, L, 4)
+        dirty = data.copy()
+        dirty[123 * L + 5] ^= 1
+        st = ctx.Stream(gpuhash.SHA1 | gpuhash.MD5, L, total, expected)
+        with pytest.raises(gpuhash.GpuHashError):  # one-shot calls are refused while a stream is open
+            ctx.HashParts([b"abc"], 3, gpuhash.SHA1)
+        off, windows = 0, 0
+        while True:
+            buf = st.acquire()
+            if buf is None:
+                break
+            assert len(buf) % L == 0 or off + len(buf) == total
+            buf[:] = dirty[off:off + len(buf)]
+            off += len(buf)
+            st.submit()
+            windows += 1
+        assert off == total and windows == 8
+        bitmap, outs, nbad = st.finish()
+        assert nbad == 1 and [i for i, b in enumerate(_bits(bitmap, 501)) if not b] == [123]
+        assert np.array_equal(outs[gpuhash.SHA1], oracle.hash_msgs(oracle.SHA1, dirty, L, 4))
+        assert np.array_equal(outs[gpuhash.MD5], oracle.hash_msgs(oracle.MD5, dirty, L, 4))
+        # the context is usable again
+        assert ctx.HashParts([b"abc"], 3, gpuhash.SHA1)[gpuhash.SHA1][0].tobytes() == hashlib.sha1(b"abc").digest()
+        # a message longer than a slot is refused
+        with pytest.raises(gpuhash.GpuHashError) as e:
+            ctx.Stream(gpuhash.SHA1, (1 << 20) + 64, 10 << 20)
+        assert e.value.status == gpuhash.GH_ERANGE
+        # abort releases the context
+        st = ctx.Stream(gpuhash.SHA256, L, total)
+        st.acquire()
+        st.abort()
+        got = ctx.HashParts([data], L, gpuhash.SHA256)[gpuhash.SHA256]
+        assert np.array_equal(got, oracle.hash_msgs(oracle.SHA256, data, L, 4))
+    finally:
+        ctx.close()
