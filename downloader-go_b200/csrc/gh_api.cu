@@ -338,6 +338,39 @@ struct SpanIndex {
     }
 };
 
+// [lo, hi) of the pinned allocation that contains p, or false. cudaPointerGetAttributes costs a few
+// microseconds; with thousands of spans cut from a few pinned buffers (10 000 small files) asking once
+// per allocation instead of once per span is worth ~40 ms per call.
+bool pinned_range(const void* p, uintptr_t* lo, uintptr_t* hi) {
+    cudaPointerAttributes a{};
+    const bool pinned = cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost;
+    cudaGetLastError();  // older drivers flag unregistered memory as an error; clear it
+    if (!pinned) return false;
+    *lo = reinterpret_cast<uintptr_t>(p);
+    *hi = *lo + 1;
+    typedef int (*GetAttrFn)(void*, int, unsigned long long);
+    static GetAttrFn get_attr = [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<GetAttrFn>(f);
+    }();
+    if (get_attr) {
+        unsigned long long start = 0;
+        size_t size = 0;
+        const unsigned long long addr = reinterpret_cast<uintptr_t>(p);
+        // CU_POINTER_ATTRIBUTE_RANGE_START_ADDR = 11, CU_POINTER_ATTRIBUTE_RANGE_SIZE = 12
+        if (get_attr(&start, 11, addr) == 0 && get_attr(&size, 12, addr) == 0 && start && size && start <= addr &&
+            addr < start + size) {
+            *lo = static_cast<uintptr_t>(start);
+            *hi = *lo + size;
+        }
+    }
+    return true;
+}
+
 void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
     ix->n = n;
     ix->ptr.resize(n);
@@ -346,15 +379,25 @@ void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
     ix->start.resize(n + 1);
     ix->pinned.resize(n);
     uint64_t off = 0;
+    uintptr_t known_lo = 0, known_hi = 0;  // the pinned allocation the previous span was found in
     for (size_t i = 0; i < n; i++) {
         ix->start[i] = off;
         off += spans[i].len;
         ix->ptr[i] = static_cast<const uint8_t*>(spans[i].host_ptr);
-        cudaPointerAttributes a{};
         bool pinned = false;
-        if (spans[i].len && cudaPointerGetAttributes(&a, spans[i].host_ptr) == cudaSuccess)
-            pinned = a.type == cudaMemoryTypeHost;
-        cudaGetLastError();  // older drivers flag unregistered memory as an error; clear it
+        if (spans[i].len) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(spans[i].host_ptr);
+            if (a >= known_lo && a + spans[i].len <= known_hi) {
+                pinned = true;
+            } else if (pinned_range(spans[i].host_ptr, &known_lo, &known_hi)) {
+                // trust the range only if the whole span lies in it; a span reaching past a registered
+                // region is staged like pageable memory
+                pinned = a + spans[i].len <= known_hi || known_hi == known_lo + 1;
+                if (known_hi == known_lo + 1) known_lo = known_hi = 0;
+            } else {
+                known_lo = known_hi = 0;
+            }
+        }
         ix->pinned[i] = pinned;
     }
     ix->start[n] = off;

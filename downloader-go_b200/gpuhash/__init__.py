@@ -212,6 +212,21 @@ class PinnedBuffer:
             self.ptr = None
 
 
+class SpanList:
+    """A prebuilt gh_span array over a list of byte buffers (keeps them alive). Building it costs a few
+    microseconds per buffer in Python; callers that verify the same files repeatedly build it once."""
+
+    def __init__(self, files):
+        self.arrs = [_u8(f) for f in files]
+        self.n = len(self.arrs)
+        self.sp = (Span * max(self.n, 1))()
+        self.total = 0
+        for i, a in enumerate(self.arrs):
+            self.sp[i].host_ptr = a.ctypes.data if a.size else None
+            self.sp[i].len = a.size
+            self.total += a.size
+
+
 class Stream:
     """gh_stream_*: feed a payload window by window into the pinned ring.
 
@@ -304,14 +319,8 @@ class Context:
     # ---- host-buffer API (names as in the Go package) ------------------------------------
     @staticmethod
     def _spans(files):
-        arrs = [_u8(f) for f in files]
-        sp = (Span * max(len(arrs), 1))()
-        total = 0
-        for i, a in enumerate(arrs):
-            sp[i].host_ptr = a.ctypes.data if a.size else None
-            sp[i].len = a.size
-            total += a.size
-        return arrs, sp, total
+        sl = files if isinstance(files, SpanList) else SpanList(files)
+        return sl.arrs, sl.sp, sl.total
 
     def VerifyPieces(self, files, piece_len, expected=None, want_digests=True):
         """files: list of byte buffers (the torrent's files in info order). Returns
