@@ -372,35 +372,42 @@ bool pinned_range(const void* p, uintptr_t* lo, uintptr_t* hi) {
 }
 
 void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
-    ix->n = n;
-    ix->ptr.resize(n);
-    ix->fd.assign(n, -1);
-    ix->is_file.assign(n, 0);
-    ix->start.resize(n + 1);
-    ix->pinned.resize(n);
+    ix->ptr.clear();
+    ix->start.clear();
+    ix->pinned.clear();
     uint64_t off = 0;
     uintptr_t known_lo = 0, known_hi = 0;  // the pinned allocation the previous span was found in
     for (size_t i = 0; i < n; i++) {
-        ix->start[i] = off;
-        off += spans[i].len;
-        ix->ptr[i] = static_cast<const uint8_t*>(spans[i].host_ptr);
+        if (!spans[i].len) continue;
+        const uint8_t* p = static_cast<const uint8_t*>(spans[i].host_ptr);
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
         bool pinned = false;
-        if (spans[i].len) {
-            const uintptr_t a = reinterpret_cast<uintptr_t>(spans[i].host_ptr);
-            if (a >= known_lo && a + spans[i].len <= known_hi) {
-                pinned = true;
-            } else if (pinned_range(spans[i].host_ptr, &known_lo, &known_hi)) {
-                // trust the range only if the whole span lies in it; a span reaching past a registered
-                // region is staged like pageable memory
-                pinned = a + spans[i].len <= known_hi || known_hi == known_lo + 1;
-                if (known_hi == known_lo + 1) known_lo = known_hi = 0;
-            } else {
-                known_lo = known_hi = 0;
-            }
+        if (a >= known_lo && a + spans[i].len <= known_hi) {
+            pinned = true;
+        } else if (pinned_range(p, &known_lo, &known_hi)) {
+            // trust the range only if the whole span lies in it; a span reaching past a registered
+            // region is staged like pageable memory
+            pinned = a + spans[i].len <= known_hi || known_hi == known_lo + 1;
+            if (known_hi == known_lo + 1) known_lo = known_hi = 0;
+        } else {
+            known_lo = known_hi = 0;
         }
-        ix->pinned[i] = pinned;
+        // Files read back to back into one arena are one run of bytes: merge spans that continue the
+        // previous one in memory, so 10 000 small files cost a handful of DMAs per window, not 10 000.
+        if (!ix->ptr.empty() && ix->pinned.back() == static_cast<char>(pinned) &&
+            ix->ptr.back() + (off - ix->start.back()) == p) {
+            off += spans[i].len;
+            continue;
+        }
+        ix->ptr.push_back(p);
+        ix->start.push_back(off);
+        ix->pinned.push_back(pinned);
+        off += spans[i].len;
     }
-    ix->start[n] = off;
+    ix->n = ix->ptr.size();
+    ix->start.push_back(off);
+    ix->fd.assign(ix->n, -1);
+    ix->is_file.assign(ix->n, 0);
 }
 
 void build_index_files(const gh_file* files, size_t n, SpanIndex* ix) {
