@@ -229,3 +229,205 @@ func PinnedFree(b []byte) {
 		C.gh_host_free(unsafe.Pointer(&b[0]))
 	}
 }
+
+// ---------------------------------------------------------------------------------------------
+// File-backed sources, metainfo and the incremental feed (gh_verify_files, gh_hash_file_parts,
+// gh_metainfo_*, gh_verify_torrent, gh_stream_*). Same caveat as above: source only.
+
+// File names one file of the payload and the length the metainfo (or stat) promises for it.
+type File struct {
+	Path string
+	Len  int64
+}
+
+func cfiles(files []File) (*C.gh_file, C.size_t, func()) {
+	n := len(files)
+	if n == 0 {
+		return nil, 0, func() {}
+	}
+	arr := (*C.gh_file)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(C.gh_file{}))))
+	sl := unsafe.Slice(arr, n)
+	for i, f := range files {
+		sl[i].path = C.CString(f.Path)
+		sl[i].len = C.uint64_t(f.Len)
+	}
+	return arr, C.size_t(n), func() {
+		for i := range sl {
+			C.free(unsafe.Pointer(sl[i].path))
+		}
+		C.free(unsafe.Pointer(arr))
+	}
+}
+
+// VerifyFiles is VerifyPieces for payload on disk: the library preads the files into its pinned
+// ring itself, so no payload byte crosses cgo.
+func (h *Hasher) VerifyFiles(files []File, pieceLen int64, expected []byte) (bitmap []uint64, digests []byte, bad uint64, err error) {
+	var total int64
+	for _, f := range files {
+		total += f.Len
+	}
+	if pieceLen <= 0 {
+		return nil, nil, 0, errors.New("gpuhash: piece length must be > 0")
+	}
+	n := (total + pieceLen - 1) / pieceLen
+	bitmap = make([]uint64, (n+63)/64)
+	digests = make([]byte, 20*n)
+	arr, cnt, free := cfiles(files)
+	defer free()
+	var exp, dig *C.uint8_t
+	var bm *C.uint64_t
+	if len(expected) > 0 {
+		exp = (*C.uint8_t)(unsafe.Pointer(&expected[0]))
+	}
+	if n > 0 {
+		dig = (*C.uint8_t)(unsafe.Pointer(&digests[0]))
+		bm = (*C.uint64_t)(unsafe.Pointer(&bitmap[0]))
+	}
+	var nbad C.uint64_t
+	rc := C.gh_verify_files(h.ctx, arr, cnt, C.uint64_t(pieceLen), exp, dig, bm, &nbad)
+	return bitmap, digests, uint64(nbad), status(h.ctx, rc, "gh_verify_files")
+}
+
+// HashFileParts is HashParts for files on disk (what uploader.go:73-89 hands to minio).
+func (h *Hasher) HashFileParts(files []File, partLen int64, algos Algo) ([]PartSum, error) {
+	var total int64
+	for _, f := range files {
+		total += f.Len
+	}
+	if partLen <= 0 {
+		return nil, errors.New("gpuhash: part length must be > 0")
+	}
+	n := int((total + partLen - 1) / partLen)
+	var s1, m5, s2 []byte
+	ptr := func(b []byte) *C.uint8_t {
+		if len(b) == 0 {
+			return nil
+		}
+		return (*C.uint8_t)(unsafe.Pointer(&b[0]))
+	}
+	if algos&SHA1 != 0 {
+		s1 = make([]byte, 20*n)
+	}
+	if algos&MD5 != 0 {
+		m5 = make([]byte, 16*n)
+	}
+	if algos&SHA256 != 0 {
+		s2 = make([]byte, 32*n)
+	}
+	arr, cnt, free := cfiles(files)
+	defer free()
+	rc := C.gh_hash_file_parts(h.ctx, arr, cnt, C.uint64_t(partLen), C.int(algos), ptr(s1), ptr(m5), ptr(s2))
+	if err := status(h.ctx, rc, "gh_hash_file_parts"); err != nil {
+		return nil, err
+	}
+	out := make([]PartSum, n)
+	for i := range out {
+		if s1 != nil {
+			out[i].SHA1 = s1[20*i : 20*i+20]
+		}
+		if m5 != nil {
+			out[i].MD5 = m5[16*i : 16*i+16]
+		}
+		if s2 != nil {
+			out[i].SHA256 = s2[32*i : 32*i+32]
+		}
+	}
+	return out, nil
+}
+
+// Metainfo is a parsed BEP 3 info dictionary.
+type Metainfo struct{ m *C.gh_metainfo }
+
+// ParseMetainfo accepts a whole .torrent file or a bare info dictionary.
+func ParseMetainfo(b []byte) (*Metainfo, error) {
+	if len(b) == 0 {
+		return nil, errors.New("gpuhash: empty metainfo")
+	}
+	var m *C.gh_metainfo
+	errbuf := make([]byte, 256)
+	rc := C.gh_metainfo_parse((*C.uint8_t)(unsafe.Pointer(&b[0])), C.size_t(len(b)), &m, (*C.char)(unsafe.Pointer(&errbuf[0])), 256)
+	if rc != C.GH_OK {
+		return nil, fmt.Errorf("gpuhash: bad metainfo: %s", C.GoString((*C.char)(unsafe.Pointer(&errbuf[0]))))
+	}
+	mi := &Metainfo{m}
+	runtime.SetFinalizer(mi, func(x *Metainfo) { C.gh_metainfo_free(x.m) })
+	return mi, nil
+}
+
+func (m *Metainfo) PieceLength() int64 { return int64(C.gh_metainfo_piece_length(m.m)) }
+func (m *Metainfo) NumPieces() int     { return int(C.gh_metainfo_n_pieces(m.m)) }
+func (m *Metainfo) Pieces() []byte {
+	return C.GoBytes(unsafe.Pointer(C.gh_metainfo_pieces(m.m)), C.int(20*m.NumPieces()))
+}
+
+// VerifyTorrent verifies the files laid out under baseDir (anacrolix file-storage layout) against
+// the metainfo's piece hashes in one batched call.
+func (h *Hasher) VerifyTorrent(m *Metainfo, baseDir string) (bitmap []uint64, digests []byte, bad uint64, err error) {
+	n := m.NumPieces()
+	bitmap = make([]uint64, (n+63)/64)
+	digests = make([]byte, 20*n)
+	dir := C.CString(baseDir)
+	defer C.free(unsafe.Pointer(dir))
+	var dig *C.uint8_t
+	var bm *C.uint64_t
+	if n > 0 {
+		dig = (*C.uint8_t)(unsafe.Pointer(&digests[0]))
+		bm = (*C.uint64_t)(unsafe.Pointer(&bitmap[0]))
+	}
+	var nbad C.uint64_t
+	rc := C.gh_verify_torrent(h.ctx, m.m, dir, dig, bm, &nbad)
+	return bitmap, digests, uint64(nbad), status(h.ctx, rc, "gh_verify_torrent")
+}
+
+// Stream feeds a payload window by window into the library's pinned ring.
+type Stream struct {
+	h  *Hasher
+	st *C.gh_stream
+	n  int64
+	al Algo
+}
+
+func (h *Hasher) NewStream(algos Algo, msgLen, total int64, expected []byte) (*Stream, error) {
+	var exp *C.uint8_t
+	if len(expected) > 0 {
+		exp = (*C.uint8_t)(unsafe.Pointer(&expected[0]))
+	}
+	s := &Stream{h: h, al: algos, n: (total + msgLen - 1) / msgLen}
+	rc := C.gh_stream_open(h.ctx, C.int(algos), C.uint64_t(msgLen), C.uint64_t(total), exp, &s.st)
+	return s, status(h.ctx, rc, "gh_stream_open")
+}
+
+// Acquire returns the next pinned window (C memory, valid until Submit) or nil when all bytes were fed.
+func (s *Stream) Acquire() ([]byte, error) {
+	var buf unsafe.Pointer
+	var cap_ C.uint64_t
+	if rc := C.gh_stream_acquire(s.st, &buf, &cap_); rc != C.GH_OK {
+		return nil, status(s.h.ctx, rc, "gh_stream_acquire")
+	}
+	if cap_ == 0 {
+		return nil, nil
+	}
+	return unsafe.Slice((*byte)(buf), int(cap_)), nil
+}
+
+func (s *Stream) Submit(window []byte) error {
+	return status(s.h.ctx, C.gh_stream_submit(s.st, C.uint64_t(len(window))), "gh_stream_submit")
+}
+
+// Finish waits for the device and returns the SHA-1 digests, the pass bitmap and the number of
+// failed pieces (for streams opened with SHA1 and expected hashes).
+func (s *Stream) Finish() (bitmap []uint64, sha1 []byte, bad uint64, err error) {
+	bitmap = make([]uint64, (s.n+63)/64)
+	var d *C.uint8_t
+	if s.al&SHA1 != 0 && s.n > 0 {
+		sha1 = make([]byte, 20*s.n)
+		d = (*C.uint8_t)(unsafe.Pointer(&sha1[0]))
+	}
+	var bm *C.uint64_t
+	if s.n > 0 {
+		bm = (*C.uint64_t)(unsafe.Pointer(&bitmap[0]))
+	}
+	var nbad C.uint64_t
+	rc := C.gh_stream_finish(s.st, d, nil, nil, bm, &nbad)
+	return bitmap, sha1, uint64(nbad), status(s.h.ctx, rc, "gh_stream_finish")
+}
