@@ -67,8 +67,13 @@ __device__ __forceinline__ void sha1_compress(uint32_t (&s)[5], uint32_t (&w)[16
         else             { f = f_xor3(b, c, d); k = 0xca62c1d6u; }
         uint32_t tmp;
         if constexpr (FMA_ADDS) {
-            // (wt + k) and (+ e) are off the critical path; the last add fuses with rotl5 into LEA.HI
-            tmp = rotl(a, 5) + addf<true>(addf<true>(addf<true>(wt, k, one), e, one), f, one);
+            // e + k is known four rounds ahead and wt one schedule step ahead: (e + k) + wt as two
+            // FMA-pipe adds whose only late input, wt, is a single IMAD away from the result. The add
+            // of f stays a plain add (ptxas may not re-associate across the IMAD), and the last add
+            // fuses with rotl5 into LEA.HI, so the chain through a is unchanged while the ALU pipe
+            // sheds one instruction per round.
+            const uint32_t pre = addf<true>(wt, e + k, one);
+            tmp = rotl(a, 5) + (f + pre);
         } else {
             tmp = rotl(a, 5) + f + (e + k + wt);
         }

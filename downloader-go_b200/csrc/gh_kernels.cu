@@ -713,9 +713,10 @@ int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return v && *v ? atoi(v) : dflt;
 }
-// -1 = per-algorithm default (measured): SHA-1 keeps its adds on the ALU pipe (the FMA hop lengthens the
-// lone-warp chain by 17 % and buys 1 % when saturated), SHA-256 moves them (+12..15 %), fused
-// MD5+SHA-256 moves them only when warps are plentiful.
+// -1 = per-algorithm default (measured on B200, profiles/r01_ab_*.jsonl): SHA-1 moves its off-chain
+// adds to the FMA pipe (+10..13 % both for a lone warp and saturated), SHA-256 moves all of them
+// (+12..15 % saturated; lone warps use the role-split kernels instead), fused MD5+SHA-256 only when
+// warps are plentiful.
 int fma_adds_override() {
     static const int v = env_int("GPUHASH_FMA_ADDS", -1);
     return v;
@@ -767,7 +768,7 @@ cudaError_t launch_range(const GhJob& job_in, uint64_t first, uint64_t count, bo
     const uint64_t nblocks = (warps + wpb - 1) / wpb;
     if (nblocks > 0x7fffffffull) return cudaErrorInvalidValue;
     const unsigned blocks = static_cast<unsigned>(nblocks);
-    bool fma = ALGOS == GH_SHA256 || (ALGOS == (GH_MD5 | GH_SHA256) && wpb > 1);
+    bool fma = ALGOS == GH_SHA1 || ALGOS == GH_SHA256 || (ALGOS == (GH_MD5 | GH_SHA256) && wpb > 1);
     if (ALGOS == GH_MD5) fma = false;  // MD5 has no FMA variant
     if (fma_adds_override() >= 0 && ALGOS != GH_MD5) fma = fma_adds_override() != 0;
     if (staged) {
