@@ -815,7 +815,11 @@ int gh_create(gh_ctx** out, const gh_config* cfg) {
     int nd = cfg && cfg->n_devices > 0 ? cfg->n_devices : count;
     if (cfg && cfg->slot_bytes) c->slot_bytes = (cfg->slot_bytes + 255) & ~255ull;
     if (cfg && cfg->slots) c->n_slots = std::max(2, cfg->slots);
-    const int st = cfg && cfg->stage_threads > 0 ? cfg->stage_threads : kDefaultStageThreads;
+    // default: one staging thread per host core, between 4 and 16 (pread/memcpy into the pinned ring
+    // scales to ~44 GB/s at 16 threads on the test box, 26 GB/s at 4)
+    int st = static_cast<int>(std::thread::hardware_concurrency());
+    st = std::max(kDefaultStageThreads, std::min(16, st));
+    if (cfg && cfg->stage_threads > 0) st = cfg->stage_threads;
     for (int i = 0; i < nd; i++) {
         const int ord = (cfg && cfg->devices && cfg->n_devices > 0) ? cfg->devices[i] : i;
         if (ord < 0 || ord >= count) {

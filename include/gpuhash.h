@@ -54,7 +54,7 @@ typedef struct {
     const int* devices;       /* CUDA ordinals, NULL = 0..n_devices-1 */
     uint64_t   slot_bytes;    /* device bytes per ring slot, 0 = default (256 MiB) */
     int        slots;         /* ring slots per device, 0 = default (4), minimum 2 */
-    int        stage_threads; /* host threads copying pageable spans into the pinned ring, 0 = default (4) */
+    int        stage_threads; /* host threads copying pageable spans / reading files into the pinned ring, 0 = default (one per core, 4..16) */
 } gh_config;
 
 /* A run of stream bytes in host memory. The logical stream is the concatenation of the spans, in
