@@ -425,3 +425,33 @@ def test_incremental_stream_feed():
         assert np.array_equal(got, oracle.hash_msgs(oracle.SHA256, data, L, 4))
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("piece_len,total", [(1, 5000), (7, 7 * 3000 + 3), (63, 63 * 40), (64, 64), (4096, 100), (4096, 4096),
+                                             (16, 16 * 33), (1 << 20, (1 << 20) + 1), (48, 48 * 1025)])
+def test_extreme_piece_shapes(gh, piece_len, total):
+    """One-byte pieces, a stream shorter than one piece, exactly one piece, 33 pieces (two warps),
+    lengths that are multiples of 16 but not of 64 (TMA rows with a sub-block tail)."""
+    data = oracle.gen(31, 1, total)
+    expected = oracle.hash_msgs(oracle.SHA1, data, piece_len, 4)
+    bitmap, dig, nbad = gh.VerifyPieces([data], piece_len, expected)
+    assert nbad == 0 and np.array_equal(dig, expected)
+    n = expected.shape[0]
+    assert all(_bits(bitmap, n)) and not any(_bits(bitmap, bitmap.size * 64)[n:])
+    both = gh.HashParts([data], piece_len, gpuhash.MD5 | gpuhash.SHA256)
+    assert np.array_equal(both[gpuhash.MD5], oracle.hash_msgs(oracle.MD5, data, piece_len, 4))
+    assert np.array_equal(both[gpuhash.SHA256], oracle.hash_msgs(oracle.SHA256, data, piece_len, 4))
+
+
+def test_single_long_message_through_small_ring():
+    """One 9 MiB message, ring windows of 1 MiB: a group of one chain, nine chained launches."""
+    ctx = gpuhash.Context(devices=[0], slot_bytes=1 << 20, slots=2)
+    try:
+        n = 9 * (1 << 20) + 77
+        data = oracle.gen(12, 0, n)
+        got = ctx.HashParts([data, b"", data[:5]], n + 5, gpuhash.SHA1 | gpuhash.MD5 | gpuhash.SHA256)
+        whole = np.concatenate([data, data[:5]])
+        for alg, _ in ALGS:
+            assert got[alg][0].tobytes() == oracle.digest(alg, whole)
+    finally:
+        ctx.close()
