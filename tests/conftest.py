@@ -12,6 +12,12 @@ for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "downloader-go_
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # a fresh checkout has no built artefacts (they are git-ignored): build them once, in-tree
+    lib = os.path.join(ROOT, "downloader-go_b200", "libgpuhash.so")
+    ora = os.path.join(ROOT, "oracle", "libgh_oracle.so")
+    if not (os.path.exists(lib) and os.path.exists(ora)):
+        import __graft_entry__
+        __graft_entry__.build()
 
 
 @pytest.fixture(scope="session")
