@@ -63,3 +63,17 @@ def test_shard_ranges_partition_on_word_boundaries(n, shards):
     sizes = [gpuhash.shard_range(n, shards, s) for s in range(shards)]
     words = [(e - b + 63) // 64 for b, e in sizes]
     assert max(words) - min(words) <= 1
+
+
+def test_header_is_plain_c_and_example_links(tmp_path):
+    """include/gpuhash.h is the FFI contract: it must compile as C99 (cgo and any C caller see it
+    that way), and the plain-C example must link against the shared library with nothing else."""
+    import subprocess
+    exe = str(tmp_path / "verify_torrent")
+    cmd = ["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "examples", "verify_torrent.c"), "-L" + os.path.dirname(gpuhash.LIB_PATH), "-lgpuhash",
+           "-Wl,-rpath," + os.path.dirname(gpuhash.LIB_PATH), "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr

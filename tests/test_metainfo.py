@@ -145,3 +145,26 @@ def test_hash_file_parts_matches_buffers(gh, tmp_path):
         assert np.array_equal(got[gpuhash.MD5], oracle.hash_msgs(oracle.MD5, data, 3 << 19))
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_c_example_verifies_a_torrent_on_disk(tmp_path):
+    """examples/verify_torrent.c, compiled with gcc -std=c99, against a payload with one bad piece."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "verify_torrent")
+    libdir = os.path.dirname(gpuhash.LIB_PATH)
+    subprocess.check_call(["gcc", "-std=c99", "-I" + os.path.join(root, "include"), os.path.join(root, "examples", "verify_torrent.c"),
+                           "-L" + libdir, "-lgpuhash", "-Wl,-rpath," + libdir, "-o", exe])
+    data = oracle.gen(2, 0, 300000)
+    info = make_info("clip.mkv", 16384, None, data.tobytes())
+    tor = tmp_path / "clip.torrent"
+    tor.write_bytes(benc({"announce": "http://t.invalid/a", "info": info}))
+    (tmp_path / "clip.mkv").write_bytes(data.tobytes())
+    r = subprocess.run([exe, str(tor), str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0 and "0 bad piece(s)" in r.stdout and hashlib.sha1(benc(info)).hexdigest() in r.stdout, r.stdout + r.stderr
+    bad = bytearray(data.tobytes())
+    bad[5 * 16384 + 9] ^= 4
+    (tmp_path / "clip.mkv").write_bytes(bytes(bad))
+    r = subprocess.run([exe, str(tor), str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 1 and "piece 5 failed" in r.stdout and "1 bad piece(s)" in r.stdout, r.stdout + r.stderr
