@@ -162,10 +162,10 @@ def run_reference(args):
     probe = np.empty(64 * PIECE_LEN, dtype=np.uint8)
     parallel_gen(oracle, SEED, 0, probe, threads)
     rate, _ = cpu_rate(oracle, probe, PIECE_LEN, threads)
-    want = int(rate * 1e9 * 2.0)  # ~2 s of CPU work per step
+    want = int(rate * 1e9 * float(os.environ.get("GH_BENCH_REF_STEP_SECONDS", "2.0")))  # CPU work per step
     avail = mem_available()
     cap = max(1 << 30, min(16 << 30, avail // 4 if avail else 4 << 30))
-    sample = max(64 * PIECE_LEN, min(cap, want) // PIECE_LEN * PIECE_LEN)
+    sample = max(16 * PIECE_LEN, min(cap, want) // PIECE_LEN * PIECE_LEN)
     data = np.empty(sample, dtype=np.uint8)
     parallel_gen(oracle, SEED, 0, data, threads)
     expected = oracle.hash_msgs(oracle.SHA1, data, PIECE_LEN, threads)

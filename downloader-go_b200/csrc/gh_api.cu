@@ -735,6 +735,12 @@ int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8
         c->stats.wall_ms = 0;
         return GH_OK;
     }
+    // n_bad is counted from the bitmap: keep a private one when the caller wants only the count
+    std::vector<uint64_t> own_bitmap;
+    if (!bitmap && n_bad && expected && (algos & GH_SHA1)) {
+        own_bitmap.assign((n + 63) / 64 + 1, 0);
+        bitmap = own_bitmap.data();
+    }
     BatchArgs A{&ix, msg_len, algos, expected, {sha1_out, md5_out, sha256_out}, bitmap, n};
     const int nd = static_cast<int>(c->devs.size());
     std::vector<int> rcs(nd, GH_OK);
@@ -813,7 +819,7 @@ int gh_create(gh_ctx** out, const gh_config* cfg) {
     if (e != cudaSuccess || count == 0) return GH_ENODEVICE;  // no CPU fallback on purpose
     gh_ctx* c = new gh_ctx();
     int nd = cfg && cfg->n_devices > 0 ? cfg->n_devices : count;
-    if (cfg && cfg->slot_bytes) c->slot_bytes = (cfg->slot_bytes + 255) & ~255ull;
+    if (cfg && cfg->slot_bytes) c->slot_bytes = std::max<uint64_t>((cfg->slot_bytes + 255) & ~255ull, 1ull << 20);
     if (cfg && cfg->slots) c->n_slots = std::max(2, cfg->slots);
     // default: one staging thread per host core, between 4 and 16 (pread/memcpy into the pinned ring
     // scales to ~44 GB/s at 16 threads on the test box, 26 GB/s at 4)

@@ -52,7 +52,7 @@ enum { GH_SHA1 = 1, GH_MD5 = 2, GH_SHA256 = 4 }; /* algos bitmask; GH_MD5|GH_SHA
 typedef struct {
     int        n_devices;     /* 0 = every visible device */
     const int* devices;       /* CUDA ordinals, NULL = 0..n_devices-1 */
-    uint64_t   slot_bytes;    /* device bytes per ring slot, 0 = default (256 MiB) */
+    uint64_t   slot_bytes;    /* device bytes per ring slot, 0 = default (256 MiB), minimum 1 MiB */
     int        slots;         /* ring slots per device, 0 = default (4), minimum 2 */
     int        stage_threads; /* host threads copying pageable spans / reading files into the pinned ring, 0 = default (one per core, 4..16) */
 } gh_config;

@@ -328,6 +328,21 @@ def test_device_unaligned_base_and_stride(gh):
     assert got[0].tobytes().hex() == "27a36dfb037754434ba684bcb73fc15ff2100290"
 
 
+def test_n_bad_without_a_bitmap_buffer(gh):
+    """Callers that only want the count may pass ok_bitmap_out = NULL."""
+    import ctypes
+    L = 16384
+    data = oracle.gen(13, 0, 70 * L)
+    expected = oracle.hash_msgs(oracle.SHA1, data, L)
+    dirty = data.copy()
+    dirty[3 * L] ^= 1
+    dirty[69 * L + 5] ^= 1
+    sl = gpuhash.SpanList([dirty])
+    nbad = ctypes.c_uint64()
+    rc = gh.L.gh_verify_pieces(gh.h, sl.sp, sl.n, L, ctypes.c_void_p(expected.ctypes.data), None, None, ctypes.byref(nbad))
+    assert rc == 0 and nbad.value == 2
+
+
 def test_stats_report_launches_and_bytes(gh):
     before = gh.stats()
     data = oracle.gen(1, 0, 1 << 20)
