@@ -210,6 +210,7 @@ struct Device {
     uint8_t* d_out = nullptr;   uint64_t d_out_cap = 0;   // digests (+ expected)
     uint32_t* d_ok = nullptr;   uint64_t d_ok_cap = 0;
     uint32_t* d_state = nullptr; uint64_t d_state_cap = 0;
+    uint64_t* d_lens = nullptr;  uint64_t d_lens_cap = 0;  // per-message lengths (table batches)
     uint8_t* h_out = nullptr;   uint64_t h_out_cap = 0;   // pinned mirror of results
     std::vector<cudaEvent_t> ev_pool;                     // start/stop pairs for kernel timing
     size_t ev_used = 0;
@@ -371,7 +372,7 @@ bool pinned_range(const void* p, uintptr_t* lo, uintptr_t* hi) {
     return true;
 }
 
-void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
+void build_index(const gh_span* spans, size_t n, SpanIndex* ix, bool merge = true) {
     ix->ptr.clear();
     ix->start.clear();
     ix->pinned.clear();
@@ -394,7 +395,7 @@ void build_index(const gh_span* spans, size_t n, SpanIndex* ix) {
         }
         // Files read back to back into one arena are one run of bytes: merge spans that continue the
         // previous one in memory, so 10 000 small files cost a handful of DMAs per window, not 10 000.
-        if (!ix->ptr.empty() && ix->pinned.back() == static_cast<char>(pinned) &&
+        if (merge && !ix->ptr.empty() && ix->pinned.back() == static_cast<char>(pinned) &&
             ix->ptr.back() + (off - ix->start.back()) == p) {
             off += spans[i].len;
             continue;
@@ -477,20 +478,33 @@ int slot_begin(gh_ctx* c, Slot& s) {
 // After a window's copies: queue its kernel(s) on the compute stream behind them.
 int slot_launch(gh_ctx* c, Device& d, Slot& s, int algos, const GhJob& j);
 
+// Where each message of a batch lives in the logical stream. Uniform: message m = stream[m*L, ...),
+// only the last one short (pieces of a torrent, parts of one file). Table: explicit offset/length per
+// message (parts of MANY files in one batch: every file starts a new part, so every file's last part
+// may be short); on the device every message still owns a row of L bytes.
+struct MsgTable {
+    uint64_t L = 0, total = 0, n = 0;
+    std::vector<uint64_t> off_, len_;  // empty in the uniform case
+    bool uniform() const { return off_.empty(); }
+    uint64_t off(uint64_t m) const { return uniform() ? m * L : off_[m]; }
+    uint64_t len(uint64_t m) const { return uniform() ? std::min(L, total - m * L) : len_[m]; }
+};
+
 // Chunk-interleaved window: for every message m of the group [g0, g0+g) bring stream bytes
 // [(g0+m)*L + prior, +min(chunk, len_m - prior)) to slot offset m*chunk. Consecutive rows that lie
 // inside one span move as one strided copy (DMA for pinned spans, pooled memcpy for pageable ones);
 // a row that straddles a span (file) boundary falls back to the byte-exact 1-D gather.
-int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g, uint64_t L, uint64_t last_len,
-                uint64_t prior, uint64_t chunk) {
+int gather_rows(gh_ctx* c, const SpanIndex& ix, const MsgTable& T, Slot& s, uint64_t g0, uint64_t g, uint64_t prior,
+                uint64_t chunk) {
     uint64_t st_lo = ~0ull, st_hi = 0;
     size_t si = 0;
     uint64_t m = 0;
+    const uint64_t L = T.L;
     while (m < g) {
-        const uint64_t mlen = (m == g - 1) ? last_len : L;
+        const uint64_t mlen = T.len(g0 + m);
         if (prior >= mlen) { m++; continue; }
         const uint64_t w = std::min(chunk, mlen - prior);
-        const uint64_t lo = (g0 + m) * L + prior;
+        const uint64_t lo = T.off(g0 + m) + prior;
         while (si + 1 < ix.n && ix.start[si + 1] <= lo) si++;
         while (si > 0 && ix.start[si] > lo) si--;
         const bool inside = si < ix.n && ix.start[si] <= lo && lo + w <= ix.start[si + 1];
@@ -500,13 +514,14 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, Slot& s, uint64_t g0, uint64_t g
             m++;
             continue;
         }
-        // extend over following rows of the same width that stay inside span si
+        // extend over following rows of the same width, one message length apart, inside span si
         uint64_t rows = 1;
         while (m + rows < g) {
-            const uint64_t m2 = m + rows;
-            const uint64_t mlen2 = (m2 == g - 1) ? last_len : L;
+            const uint64_t m2 = g0 + m + rows;
+            const uint64_t mlen2 = T.len(m2);
             if (prior >= mlen2 || std::min(chunk, mlen2 - prior) != w) break;
-            if ((g0 + m2) * L + prior + w > ix.start[si + 1]) break;
+            if (T.off(m2) != T.off(m2 - 1) + L) break;
+            if (T.off(m2) + prior + w > ix.start[si + 1]) break;
             rows++;
         }
         const uint8_t* src = ix.ptr[si] + (lo - ix.start[si]);
@@ -548,6 +563,7 @@ int slot_launch(gh_ctx* c, Device& d, Slot& s, int algos, const GhJob& j) {
 // --------------------------------------------------------------------------- one device's share
 struct BatchArgs {
     const SpanIndex* ix;
+    const MsgTable* T;
     uint64_t msg_len;
     int algos;
     const uint8_t* expected;  // host, 20*n_total or null
@@ -560,9 +576,9 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
     *kernel_ms = 0;
     if (m0 >= m1) return GH_OK;
     GH_CUDA(c, cudaSetDevice(d.ordinal));
-    const uint64_t n = m1 - m0, L = A.msg_len, total = A.ix->total();
-    const uint64_t range_lo = m0 * L, range_hi = std::min(m1 * L, total);
-    const uint64_t last_len_global = total - (A.n_total - 1) * L;
+    const MsgTable& T = *A.T;
+    const uint64_t n = m1 - m0, L = A.msg_len;
+    const bool table = !T.uniform();
 
     // result layout on the device: [sha1 20n][md5 16n][sha256 32n][expected 20n], each 256-aligned
     auto al = [](uint64_t v) { return (v + 255) & ~255ull; };
@@ -579,6 +595,11 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
         GH_CUDA(c, cudaMemcpyAsync(d.d_out + o_exp, d.h_out + o_exp, 20 * n, cudaMemcpyHostToDevice, d.stream));
         GH_CUDA(c, cudaMemsetAsync(d.d_ok, 0, (ok_words + 1) * 4, d.stream));
     }
+    if (table) {  // per-message lengths for the kernels (staged through the pinned result mirror)
+        if ((rc = grow(c, &d.d_lens, &d.d_lens_cap, n * 8))) return rc;
+        std::vector<uint64_t>& hl = const_cast<MsgTable&>(T).len_;
+        GH_CUDA(c, cudaMemcpyAsync(d.d_lens, hl.data() + m0, n * 8, cudaMemcpyHostToDevice, d.stream));
+    }
     for (auto& sl : d.slots) sl.in_use = false;
     const size_t first_timing_event = d.ev_used;
 
@@ -589,7 +610,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
     job.sha256 = (A.algos & GH_SHA256) ? d.d_out + o_sha256 : nullptr;
 
     const uint64_t S = c->slot_bytes;
-    const uint64_t bytes_here = range_hi - range_lo;
+    const uint64_t bytes_here = table ? n * L : T.off(m1 - 1) + T.len(m1 - 1) - T.off(m0);
     if (bytes_here <= S || L <= kMinChunk) {
         // whole messages per window (everything fits one window, or messages are small enough that a
         // window still carries thousands of independent chains)
@@ -598,10 +619,17 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
         for (uint64_t q = m0; q < m1; q += per, b++) {
             Slot& s = d.slots[b % d.slots.size()];
             const uint64_t k = std::min(per, m1 - q);
-            const uint64_t lo = q * L, hi = std::min((q + k) * L, total);
             uint64_t st_lo = ~0ull, st_hi = 0;
             if ((rc = slot_begin(c, s))) return rc;
-            if ((rc = gather(c, *A.ix, lo, hi, s, 0, &st_lo, &st_hi))) return rc;
+            // runs of messages that follow each other in the stream at full length land back to back
+            // in the slot as well: one gather per run (the whole window in the uniform case)
+            for (uint64_t r0 = q; r0 < q + k;) {
+                uint64_t r1 = r0 + 1;
+                while (r1 < q + k && T.len(r1 - 1) == L && T.off(r1) == T.off(r1 - 1) + L) r1++;
+                if ((rc = gather(c, *A.ix, T.off(r0), T.off(r1 - 1) + T.len(r1 - 1), s, (r0 - q) * L, &st_lo, &st_hi)))
+                    return rc;
+                r0 = r1;
+            }
             if ((rc = flush_staged(c, s, st_lo, st_hi))) return rc;
             GhJob j = job;
             j.data = s.d_buf;
@@ -609,8 +637,9 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
             j.chunk_len = L;
             j.prior = 0;
             j.n_msgs = k;
-            j.last_msg_len = (q + k == A.n_total) ? last_len_global : L;
+            j.last_msg_len = T.len(q + k - 1);
             const uint64_t rel = q - m0;
+            if (table) j.lens = d.d_lens + rel;
             if (j.sha1) j.sha1 += 20 * rel;
             if (j.md5) j.md5 += 16 * rel;
             if (j.sha256) j.sha256 += 32 * rel;
@@ -632,11 +661,11 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
             const uint64_t g = std::min(gsz, m1 - g0);
             const uint64_t chunk = std::min<uint64_t>((S / g) & ~63ull, (L + 63) & ~63ull);
             const uint64_t rel = g0 - m0;
-            const uint64_t g_last_len = (g0 + g == A.n_total) ? last_len_global : L;
+            const uint64_t g_last_len = T.len(g0 + g - 1);
             for (uint64_t prior = 0; prior < L; prior += chunk, b++) {
                 Slot& s = d.slots[b % d.slots.size()];
                 if ((rc = slot_begin(c, s))) return rc;
-                if ((rc = gather_rows(c, *A.ix, s, g0, g, L, g_last_len, prior, chunk))) return rc;
+                if ((rc = gather_rows(c, *A.ix, T, s, g0, g, prior, chunk))) return rc;
                 GhJob j = job;
                 j.data = s.d_buf;
                 j.stride = chunk;
@@ -645,6 +674,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
                 j.n_msgs = g;
                 j.last_msg_len = g_last_len;
                 j.state = d.d_state;  // group-local [word][g]; kernels run in order on one stream, so groups may share it
+                if (table) j.lens = d.d_lens + rel;
                 if (j.sha1) j.sha1 += 20 * rel;
                 if (j.md5) j.md5 += 16 * rel;
                 if (j.sha256) j.sha256 += 32 * rel;
@@ -688,27 +718,28 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
         float ms = 0;
         if (cudaEventElapsedTime(&ms, d.ev_pool[e], d.ev_pool[e + 1]) == cudaSuccess) *kernel_ms += ms;
     }
-    (void)range_lo; (void)range_hi;
     return GH_OK;
 }
 
 int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8_t* expected, uint8_t* sha1_out,
-              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad);
+              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad, bool per_run = false);
 
 int run_batch(gh_ctx* c, const gh_span* spans, size_t n_spans, uint64_t msg_len, int algos, const uint8_t* expected,
-              uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+              uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad,
+              bool per_file = false) {
     if (!c) return GH_EINVAL;
     std::lock_guard<std::mutex> g(c->mu);
     if (n_spans && !spans) return fail(c, GH_EINVAL, "spans is NULL");
     for (size_t i = 0; i < n_spans; i++)
         if (spans[i].len && !spans[i].host_ptr) return fail(c, GH_EINVAL, "span with NULL pointer and non-zero length");
     SpanIndex ix;
-    build_index(spans, n_spans, &ix);
-    return run_index(c, ix, msg_len, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad);
+    build_index(spans, n_spans, &ix, !per_file);
+    return run_index(c, ix, msg_len, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad, per_file);
 }
 
 int run_files(gh_ctx* c, const gh_file* files, size_t n_files, uint64_t msg_len, int algos, const uint8_t* expected,
-              uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+              uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad,
+              bool per_file = false) {
     if (!c) return GH_EINVAL;
     std::lock_guard<std::mutex> g(c->mu);
     if (n_files && !files) return fail(c, GH_EINVAL, "files is NULL");
@@ -716,19 +747,35 @@ int run_files(gh_ctx* c, const gh_file* files, size_t n_files, uint64_t msg_len,
         if (files[i].len && !files[i].path) return fail(c, GH_EINVAL, "file with NULL path and non-zero length");
     SpanIndex ix;
     build_index_files(files, n_files, &ix);
-    return run_index(c, ix, msg_len, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad);
+    return run_index(c, ix, msg_len, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad, per_file);
 }
 
-// caller holds c->mu
+// caller holds c->mu. per_run: messages restart at every run (file) of the index instead of running
+// through the concatenated stream.
 int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8_t* expected, uint8_t* sha1_out,
-              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad, bool per_run) {
     if (c->lost) return fail(c, GH_ECTX_LOST, "context lost after a device fault");
     if (c->stream_open) return fail(c, GH_EINVAL, "a gh_stream is open on this context; finish or abort it first");
     if (msg_len == 0) return fail(c, GH_EINVAL, "message length must be > 0");
     if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256)))
         return fail(c, GH_EINVAL, "algos must be a mask of GH_SHA1|GH_MD5|GH_SHA256");
     const auto t0 = std::chrono::steady_clock::now();
-    const uint64_t n = count_msgs(ix.total(), msg_len);
+    MsgTable T;
+    T.L = msg_len;
+    T.total = ix.total();
+    if (per_run) {
+        for (size_t i = 0; i < ix.n; i++) {
+            const uint64_t lo = ix.start[i], hi = ix.start[i + 1];
+            for (uint64_t o = lo; o < hi; o += msg_len) {
+                T.off_.push_back(o);
+                T.len_.push_back(std::min(msg_len, hi - o));
+            }
+        }
+        T.n = T.off_.size();
+    } else {
+        T.n = count_msgs(T.total, msg_len);
+    }
+    const uint64_t n = T.n;
     if (n_bad) *n_bad = 0;
     if (n == 0) {
         c->stats.kernel_ms = 0;
@@ -741,7 +788,7 @@ int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8
         own_bitmap.assign((n + 63) / 64 + 1, 0);
         bitmap = own_bitmap.data();
     }
-    BatchArgs A{&ix, msg_len, algos, expected, {sha1_out, md5_out, sha256_out}, bitmap, n};
+    BatchArgs A{&ix, &T, msg_len, algos, expected, {sha1_out, md5_out, sha256_out}, bitmap, n};
     const int nd = static_cast<int>(c->devs.size());
     std::vector<int> rcs(nd, GH_OK);
     std::vector<double> kms(nd, 0.0);
@@ -874,6 +921,7 @@ void gh_destroy(gh_ctx* c) {
         if (d.d_out) cudaFree(d.d_out);
         if (d.d_ok) cudaFree(d.d_ok);
         if (d.d_state) cudaFree(d.d_state);
+        if (d.d_lens) cudaFree(d.d_lens);
         if (d.h_out) cudaFreeHost(d.h_out);
         for (auto e : d.ev_pool) cudaEventDestroy(e);
         if (d.stream) cudaStreamDestroy(d.stream);
@@ -913,6 +961,16 @@ int gh_verify_files(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t 
 int gh_hash_file_parts(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t part_len, int algos,
                        uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out) {
     return run_files(ctx, files, n_files, part_len, algos, nullptr, sha1_out, md5_out, sha256_out, nullptr, nullptr);
+}
+
+int gh_hash_parts_per_file(gh_ctx* ctx, const gh_span* files, size_t n_files, uint64_t part_len, int algos,
+                           uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out) {
+    return run_batch(ctx, files, n_files, part_len, algos, nullptr, sha1_out, md5_out, sha256_out, nullptr, nullptr, true);
+}
+
+int gh_hash_file_parts_per_file(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t part_len, int algos,
+                                uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out) {
+    return run_files(ctx, files, n_files, part_len, algos, nullptr, sha1_out, md5_out, sha256_out, nullptr, nullptr, true);
 }
 
 int gh_s3_etag(gh_ctx* ctx, const uint8_t* part_md5s, uint64_t n_parts, char* out, size_t out_len) {

@@ -18,6 +18,8 @@ struct GhJob {
     uint64_t n_msgs;
     uint64_t msg_len;       // full length of every message but the last
     uint64_t last_msg_len;  // full length of message n_msgs-1
+    const uint64_t* lens;   // optional: full length of every message (<= msg_len); then msg_len/last_msg_len only
+                            // bound the loop, and every row must be addressable for its chunk (ring slots are)
     uint32_t* state;        // [GH_STATE_WORDS][n_msgs] midstates (needed only when a message spans launches)
     uint8_t* sha1;          // digests out (20 / 16 / 32 bytes per message), may be null
     uint8_t* md5;

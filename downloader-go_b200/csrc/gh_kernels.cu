@@ -256,7 +256,7 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     const uint64_t m_end = job.first_msg + job.count;
 
     const bool active = m < m_end;
-    const uint64_t total_m = active ? (m == job.n_msgs - 1 ? job.last_msg_len : job.msg_len) : 0;
+    const uint64_t total_m = !active ? 0 : job.lens ? job.lens[m] : (m == job.n_msgs - 1 ? job.last_msg_len : job.msg_len);
     const bool done_before = !active || (job.prior > 0 && job.prior >= total_m);
     const uint64_t remain = done_before ? 0 : total_m - job.prior;
     const bool ends_now = !done_before && remain <= job.chunk_len;
@@ -503,11 +503,12 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     const uint64_t common_remain = job.prior >= job.msg_len ? 0 : job.msg_len - job.prior;
     const uint32_t n_blocks = static_cast<uint32_t>((common_remain < job.chunk_len ? common_remain : job.chunk_len) >> 6);
     const uint32_t n_stages = (n_blocks + kSplitBPS - 1) / kSplitBPS;
-    const uint64_t total_m = m == job.n_msgs - 1 ? job.last_msg_len : job.msg_len;
-    const bool done_before = job.prior > 0 && job.prior >= total_m;
+    const uint64_t total_m = !active ? 0 : job.lens ? job.lens[m] : (m == job.n_msgs - 1 ? job.last_msg_len : job.msg_len);
+    const bool done_before = !active || (job.prior > 0 && job.prior >= total_m);
     const uint64_t remain = done_before ? 0 : total_m - job.prior;
     const bool ends_now = !done_before && remain <= job.chunk_len;
     const uint64_t avail = remain < job.chunk_len ? remain : job.chunk_len;
+    const uint32_t my_blocks = static_cast<uint32_t>(avail >> 6);  // == n_blocks unless a length table says less
     const uint32_t rem = ends_now ? static_cast<uint32_t>(avail & 63u) : 0u;
     const uint8_t* src = job.data + m * job.stride;
 
@@ -584,24 +585,24 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
         // ------------------------------------------------------------------ rounds warp
         Lane<ALGO, false> L;
         L.one = 1;
-        if (!done_before) {
-            if (job.prior == 0) L.init();
-            else if (active) L.load(job.state, job.n_msgs, m);
-        }
+        if (job.prior == 0 || done_before) L.init();
+        else L.load(job.state, job.n_msgs, m);
 #pragma unroll 1
         for (uint32_t jb = 0; jb < n_blocks; jb++) {
             const uint32_t wb = jb & 1u, use = jb >> 1;
             mbar_wait(w_full + 8 * wb, use & 1u);
             const uint32_t wk_addr = wk_u32 + wb * Cfg::kWkBytes + lane * 16;
-            if constexpr (ALGO == GH_SHA1) sha1_rounds(L.s1, wk_addr, job.one);
-            else sha256_rounds(L.s2, wk_addr, job.one);
+            if (jb < my_blocks) {
+                if constexpr (ALGO == GH_SHA1) sha1_rounds(L.s1, wk_addr, job.one);
+                else sha256_rounds(L.s2, wk_addr, job.one);
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive1(w_empty + 8 * wb);
         }
         bool ok = false;
         if (active && !done_before) {
             if (ends_now) {
-                finalize<ALGO, false>(L, src + static_cast<uint64_t>(n_blocks) * 64, rem, total_m);
+                finalize<ALGO, false>(L, src + static_cast<uint64_t>(my_blocks) * 64, rem, total_m);
                 ok = emit<ALGO, false>(L, job, m);
             } else {
                 L.store(job.state, job.n_msgs, m);
@@ -621,16 +622,15 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
         // ------------------------------------------------------------------ MD5 warp
         Lane<GH_MD5, false> L;
         L.one = 1;
-        if (!done_before) {
-            if (job.prior == 0) L.init();
-            else if (active) L.load(job.state, job.n_msgs, m);
-        }
+        if (job.prior == 0 || done_before) L.init();
+        else L.load(job.state, job.n_msgs, m);
         for (uint32_t s = 0; s < n_stages; s++) {
             const uint32_t b = s % kSplitStages;
             mbar_wait(tma_full + 8 * b, (s / kSplitStages) & 1u);
             const uint32_t nb = min(kSplitBPS, n_blocks - s * kSplitBPS);
 #pragma unroll 1
             for (uint32_t j = 0; j < nb; j++) {
+                if (s * kSplitBPS + j >= my_blocks) break;
                 uint32_t r[16];
                 lds_block(row_base + (b * kSplitTPS + (j >> 1)) * kTileBytes, (j & 1u) * 4u, sw, r);
                 L.absorb(r);
@@ -640,7 +640,7 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
         }
         if (active && !done_before) {
             if (ends_now) {
-                finalize<GH_MD5, false>(L, src + static_cast<uint64_t>(n_blocks) * 64, rem, total_m);
+                finalize<GH_MD5, false>(L, src + static_cast<uint64_t>(my_blocks) * 64, rem, total_m);
                 emit<GH_MD5, false>(L, job, m);
             } else {
                 L.store(job.state, job.n_msgs, m);
@@ -790,7 +790,7 @@ cudaError_t launch_algo(const GhJob& job, int sm_count, cudaStream_t stream) {
         if (job.prior >= len) return uint64_t(0);
         return len - job.prior < job.chunk_len ? len - job.prior : job.chunk_len;
     };
-    const uint64_t common = present(job.msg_len), last = present(job.last_msg_len);
+    const uint64_t common = present(job.msg_len), last = job.lens ? common : present(job.last_msg_len);
     const uint64_t inner_words = (common >> 6) * 16;
     const bool aligned = ((reinterpret_cast<uintptr_t>(job.data) | job.stride) & 15u) == 0 && job.stride < (1ull << 40);
     // The TMA rows all have the common extent; a shorter last message (BEP 3 tail piece) would make

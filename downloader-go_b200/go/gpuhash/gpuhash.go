@@ -335,6 +335,59 @@ func (h *Hasher) HashFileParts(files []File, partLen int64, algos Algo) ([]PartS
 	return out, nil
 }
 
+// HashFilePartsPerFile hashes the parts of every file of an upload job in ONE batch; parts restart at
+// every file (each file is its own S3 object). sums[i] holds file i's parts.
+func (h *Hasher) HashFilePartsPerFile(files []File, partLen int64, algos Algo) (sums [][]PartSum, err error) {
+	if partLen <= 0 {
+		return nil, errors.New("gpuhash: part length must be > 0")
+	}
+	counts := make([]int, len(files))
+	n := 0
+	for i, f := range files {
+		counts[i] = int((f.Len + partLen - 1) / partLen)
+		n += counts[i]
+	}
+	var s1, m5, s2 []byte
+	ptr := func(b []byte) *C.uint8_t {
+		if len(b) == 0 {
+			return nil
+		}
+		return (*C.uint8_t)(unsafe.Pointer(&b[0]))
+	}
+	if algos&SHA1 != 0 {
+		s1 = make([]byte, 20*n)
+	}
+	if algos&MD5 != 0 {
+		m5 = make([]byte, 16*n)
+	}
+	if algos&SHA256 != 0 {
+		s2 = make([]byte, 32*n)
+	}
+	arr, cnt, free := cfiles(files)
+	defer free()
+	rc := C.gh_hash_file_parts_per_file(h.ctx, arr, cnt, C.uint64_t(partLen), C.int(algos), ptr(s1), ptr(m5), ptr(s2))
+	if err := status(h.ctx, rc, "gh_hash_file_parts_per_file"); err != nil {
+		return nil, err
+	}
+	sums = make([][]PartSum, len(files))
+	k := 0
+	for i, c := range counts {
+		sums[i] = make([]PartSum, c)
+		for j := 0; j < c; j, k = j+1, k+1 {
+			if s1 != nil {
+				sums[i][j].SHA1 = s1[20*k : 20*k+20]
+			}
+			if m5 != nil {
+				sums[i][j].MD5 = m5[16*k : 16*k+16]
+			}
+			if s2 != nil {
+				sums[i][j].SHA256 = s2[32*k : 32*k+32]
+			}
+		}
+	}
+	return sums, nil
+}
+
 // Metainfo is a parsed BEP 3 info dictionary.
 type Metainfo struct{ m *C.gh_metainfo }
 

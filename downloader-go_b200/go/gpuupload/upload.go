@@ -25,8 +25,40 @@ import (
 // PartSize is the part length the sums are computed over (BASELINE.json config 3: 64 MiB).
 const PartSize = 64 << 20
 
+// PutAll uploads every file of a job: the part sums of ALL files come from one batched GPU call
+// (parts restart at every file), then each file goes up through the low-level multipart API.
+// keys[i] is the object key of paths[i]. Errors are returned per file, like the reference's loop
+// (uploader.go:72-92) which logs and continues.
+func PutAll(ctx context.Context, core minio.Core, h *gpuhash.Hasher, bucket string, keys, paths []string, sizes []int64) []error {
+	errs := make([]error, len(paths))
+	files := make([]gpuhash.File, len(paths))
+	for i := range paths {
+		files[i] = gpuhash.File{Path: paths[i], Len: sizes[i]}
+	}
+	sums, err := h.HashFilePartsPerFile(files, PartSize, gpuhash.MD5|gpuhash.SHA256)
+	for i := range paths {
+		if err != nil {
+			errs[i] = err
+			continue
+		}
+		errs[i] = putWithSums(ctx, core, h, bucket, keys[i], paths[i], sizes[i], sums[i])
+	}
+	return errs
+}
+
 // Put uploads one file. Files smaller than one part take minio's ordinary single PUT.
 func Put(ctx context.Context, core minio.Core, h *gpuhash.Hasher, bucket, key, path string, size int64) error {
+	if size < PartSize {
+		return putWithSums(ctx, core, h, bucket, key, path, size, nil)
+	}
+	sums, err := h.HashFileParts([]gpuhash.File{{Path: path, Len: size}}, PartSize, gpuhash.MD5|gpuhash.SHA256)
+	if err != nil {
+		return err
+	}
+	return putWithSums(ctx, core, h, bucket, key, path, size, sums)
+}
+
+func putWithSums(ctx context.Context, core minio.Core, h *gpuhash.Hasher, bucket, key, path string, size int64, sums []gpuhash.PartSum) error {
 	f, err := os.Open(path)
 	if err != nil {
 		return err
@@ -34,10 +66,6 @@ func Put(ctx context.Context, core minio.Core, h *gpuhash.Hasher, bucket, key, p
 	defer f.Close()
 	if size < PartSize {
 		_, err = core.Client.PutObjectWithContext(ctx, bucket, key, f, size, minio.PutObjectOptions{})
-		return err
-	}
-	sums, err := h.HashFileParts([]gpuhash.File{{Path: path, Len: size}}, PartSize, gpuhash.MD5|gpuhash.SHA256)
-	if err != nil {
 		return err
 	}
 	uploadID, err := core.NewMultipartUpload(bucket, key, minio.PutObjectOptions{})

@@ -73,6 +73,8 @@ ABI = {
     "gh_stream_submit": (_INT, [_VP, _U64]),
     "gh_stream_finish": (_INT, [_VP, _VP, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_stream_abort": (None, [_VP]),
+    "gh_hash_parts_per_file": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _INT, _VP, _VP, _VP]),
+    "gh_hash_file_parts_per_file": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _INT, _VP, _VP, _VP]),
     "gh_metainfo_parse": (_INT, [_VP, _SZ, ctypes.POINTER(_VP), ctypes.c_char_p, _SZ]),
     "gh_metainfo_free": (None, [_VP]),
     "gh_metainfo_piece_length": (_U64, [_VP]),
@@ -383,6 +385,24 @@ class Context:
                                        _ptr(outs.get(MD5)), _ptr(outs.get(SHA256)))
         self._check(rc, "gh_hash_file_parts")
         return outs
+
+    def HashPartsPerFile(self, files, part_len, algos):
+        """files: byte buffers, or (path, length) tuples for files on disk. Parts restart at every file.
+        Returns ({algo: uint8[n_parts_total, digest_len]}, [n_parts of each file])."""
+        on_disk = len(files) > 0 and isinstance(files[0], tuple)
+        if on_disk:
+            arr, keep, _ = self._files(files)
+            lens = [n for _, n in files]
+        else:
+            keep, arr, _ = self._spans(files)
+            lens = [a.size for a in keep]
+        counts = [count(n, part_len) for n in lens]
+        n = sum(counts)
+        outs = {a: np.zeros((n, DIGEST_LEN[a]), dtype=np.uint8) for a in (SHA1, MD5, SHA256) if algos & a}
+        fn = self.L.gh_hash_file_parts_per_file if on_disk else self.L.gh_hash_parts_per_file
+        rc = fn(self.h, arr, len(files), part_len, algos, _ptr(outs.get(SHA1)), _ptr(outs.get(MD5)), _ptr(outs.get(SHA256)))
+        self._check(rc, "gh_hash_parts_per_file")
+        return outs, counts
 
     def InfoHash(self, metainfo):
         out = np.zeros(20, dtype=np.uint8)

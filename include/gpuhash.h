@@ -171,6 +171,17 @@ int            gh_metainfo_info_hash(gh_ctx* ctx, const gh_metainfo* m, uint8_t 
 int            gh_verify_torrent(gh_ctx* ctx, const gh_metainfo* m, const char* base_dir,
                                  uint8_t* digests_out, uint64_t* ok_bitmap_out, uint64_t* n_bad_out);
 
+/* Per-file parts: every file is its own S3 object (uploader.go:72 loops over the files of a job, one
+ * PutObject each), so parts restart at every file boundary and each file's last part may be short --
+ * but ALL files of the job are hashed in ONE batch. More files mean more independent chains, which
+ * is what a GPU needs when parts are 64 MiB long (hard part 2): 24 files of
+ * 2 GiB give 768 chains instead of 32 at a time. Outputs hold file 0's parts, then file 1's, ...;
+ * file i contributes ceil(len_i / part_len) parts (none if empty). */
+int gh_hash_parts_per_file(gh_ctx* ctx, const gh_span* files, size_t n_files, uint64_t part_len, int algos,
+                           uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out);
+int gh_hash_file_parts_per_file(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64_t part_len,
+                                int algos, uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out);
+
 /* S3 multipart ETag of n binary part MD5s: hex(md5(concat)) + "-" + n (what the server returns for
  * the upload started at uploader.go:89; computed on the device like any other message).
  * out needs at least 56 bytes. */

@@ -3,6 +3,7 @@ against the CPU oracle on identical seeded inputs. Bit-exact is the bar for ever
 byte work; no tolerance). Layout follows what the reference's callers would present: pieces of a
 concatenated multi-file stream (BEP 3; torrent.go:41-106) and parts of one file (uploader.go:89)."""
 import hashlib
+import os
 
 import numpy as np
 import pytest
@@ -468,5 +469,42 @@ def test_single_long_message_through_small_ring():
         whole = np.concatenate([data, data[:5]])
         for alg, _ in ALGS:
             assert got[alg][0].tobytes() == oracle.digest(alg, whole)
+    finally:
+        ctx.close()
+
+
+@pytest.mark.parametrize("slot_mib", [0, 1])
+@pytest.mark.parametrize("algos", [gpuhash.MD5 | gpuhash.SHA256, gpuhash.SHA1 | gpuhash.MD5 | gpuhash.SHA256])
+def test_parts_per_file_batch(algos, slot_mib, tmp_path):
+    """All files of an upload job in one batch, parts restarting at every file (each file is its own
+    S3 object, uploader.go:72-89): ragged last parts, an empty file, a file shorter than one part, a
+    file that is an exact multiple; from memory and from disk; default ring and a 1 MiB ring (chunk-
+    interleaved windows with a per-message length table)."""
+    P = 300 * 1024 + 64
+    sizes = [3 * P + 17, 0, 5, 2 * P, P - 1, 7 * P + 100000, 64]
+    ctx = gpuhash.Context(devices=[0], slot_bytes=slot_mib << 20, slots=3)
+    try:
+        bufs = [oracle.gen(40 + i, 0, n) for i, n in enumerate(sizes)]
+        want = {a: [] for a, _ in ALGS}
+        for b in bufs:
+            for a, _ in ALGS:
+                if algos & a and b.size:
+                    want[a].append(oracle.hash_msgs(a, b, P, 2))
+        got, counts = ctx.HashPartsPerFile(bufs, P, algos)
+        assert counts == [4, 0, 1, 2, 1, 8, 1]
+        for a, _ in ALGS:
+            if algos & a:
+                assert np.array_equal(got[a], np.concatenate(want[a])), a
+        paths = []
+        for i, b in enumerate(bufs):
+            p = os.path.join(str(tmp_path), "f%d.bin" % i)
+            with open(p, "wb") as f:
+                f.write(b.tobytes())
+            paths.append((p, b.size))
+        got2, counts2 = ctx.HashPartsPerFile(paths, P, algos)
+        assert counts2 == counts
+        for a, _ in ALGS:
+            if algos & a:
+                assert np.array_equal(got2[a], got[a]), a
     finally:
         ctx.close()
