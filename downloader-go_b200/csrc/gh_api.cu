@@ -597,8 +597,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
     }
     if (table) {  // per-message lengths for the kernels (staged through the pinned result mirror)
         if ((rc = grow(c, &d.d_lens, &d.d_lens_cap, n * 8))) return rc;
-        std::vector<uint64_t>& hl = const_cast<MsgTable&>(T).len_;
-        GH_CUDA(c, cudaMemcpyAsync(d.d_lens, hl.data() + m0, n * 8, cudaMemcpyHostToDevice, d.stream));
+        GH_CUDA(c, cudaMemcpyAsync(d.d_lens, T.len_.data() + m0, n * 8, cudaMemcpyHostToDevice, d.stream));
     }
     for (auto& sl : d.slots) sl.in_use = false;
     const size_t first_timing_event = d.ev_used;
