@@ -20,8 +20,8 @@
         }                                                                             \
     } while (0)
 
-enum { OP_IADD3, OP_LOP3, OP_SHF, OP_PRMT, OP_IMAD, OP_LOP3_IMAD, OP_ALU_MIX, OP_SHA1, OP_MD5, OP_SHA256, OP_SHA1_FMA, OP_SHA256_FMA, OP_COUNT };
-static const char* kNames[OP_COUNT] = {"iadd3", "lop3", "shf", "prmt", "imad", "lop3+imad", "shf+lop3+iadd3",
+enum { OP_IADD3, OP_LOP3, OP_SHF, OP_PRMT, OP_IMAD, OP_LOP3_IMAD, OP_ALU_MIX, OP_IMADHI, OP_LEAHI, OP_ROT_FMA, OP_SHA1, OP_MD5, OP_SHA256, OP_SHA1_FMA, OP_SHA256_FMA, OP_COUNT };
+static const char* kNames[OP_COUNT] = {"iadd3", "lop3", "shf", "prmt", "imad", "lop3+imad", "shf+lop3+iadd3", "imad.hi", "rotl+add (lea.hi)", "rotr via imad+imad.hi",
                                        "sha1_block", "md5_block", "sha256_block", "sha1_block_fma_adds", "sha256_block_fma_adds"};
 
 template <int OP>
@@ -37,6 +37,9 @@ __device__ __forceinline__ void body(uint32_t (&x)[8], uint32_t a, uint32_t b) {
             if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x[i]) : "r"(a), "r"(b));
             else asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[i]) : "r"(a), "r"(b));
         }
+        if (OP == OP_IMADHI) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(x[i]) : "r"(a), "r"(b));
+        if (OP == OP_LEAHI) asm volatile("{.reg .u32 t; shf.l.wrap.b32 t, %0, %0, 5; add.u32 %0, t, %1;}" : "+r"(x[i]) : "r"(a));
+        if (OP == OP_ROT_FMA) asm volatile("{.reg .u32 t; mul.lo.u32 t, %0, %1; mad.hi.u32 %0, %0, %1, t;}" : "+r"(x[i]) : "r"(a));
         if (OP == OP_ALU_MIX) {
             if (i % 3 == 0) asm volatile("shf.l.wrap.b32 %0, %0, %0, 5;" : "+r"(x[i]));
             else if (i % 3 == 1) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[i]) : "r"(a), "r"(b));
@@ -149,7 +152,10 @@ int main(int argc, char** argv) {
     report<OP_PRMT>(sms, d_out, d_cyc, false);
     report<OP_IMAD>(sms, d_out, d_cyc, false);
     report<OP_LOP3_IMAD>(sms, d_out, d_cyc, false);
-    report<OP_ALU_MIX>(sms, d_out, d_cyc, true);
+    report<OP_ALU_MIX>(sms, d_out, d_cyc, false);
+    report<OP_IMADHI>(sms, d_out, d_cyc, false);
+    report<OP_LEAHI>(sms, d_out, d_cyc, false);
+    report<OP_ROT_FMA>(sms, d_out, d_cyc, true);
     printf(" },\n \"compress_by_threads_per_sm\": {\n");
     report<OP_SHA1>(sms, d_out, d_cyc, false);
     report<OP_MD5>(sms, d_out, d_cyc, false);
