@@ -179,13 +179,13 @@ class Metainfo:
         self.piece_length = int(L.gh_metainfo_piece_length(h))
         self.n_pieces = int(L.gh_metainfo_n_pieces(h))
         self.total_length = int(L.gh_metainfo_total_length(h))
-        self.name = L.gh_metainfo_name(h).decode()
+        self.name = os.fsdecode(L.gh_metainfo_name(h))  # bytes from the wire: not necessarily UTF-8
         self.pieces = ctypes.string_at(L.gh_metainfo_pieces(h), 20 * self.n_pieces) if self.n_pieces else b""
         self.files = []
         for i in range(L.gh_metainfo_n_files(h)):
             p, n = ctypes.c_char_p(), ctypes.c_uint64()
             L.gh_metainfo_file(h, i, ctypes.byref(p), ctypes.byref(n))
-            self.files.append((p.value.decode(), int(n.value)))
+            self.files.append((os.fsdecode(p.value), int(n.value)))
 
     def close(self):
         if getattr(self, "h", None):

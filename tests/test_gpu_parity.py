@@ -508,3 +508,27 @@ def test_parts_per_file_batch(algos, slot_mib, tmp_path):
                 assert np.array_equal(got2[a], got[a]), a
     finally:
         ctx.close()
+
+
+def test_randomised_shapes_against_oracle(gh):
+    """Seeded random batches: message length, total, algorithm mask and the way the stream is cut into
+    spans (including empty ones) are all drawn at random; every digest must equal the oracle's."""
+    rng = np.random.default_rng(2024)
+    masks = [gpuhash.SHA1, gpuhash.MD5, gpuhash.SHA256, gpuhash.MD5 | gpuhash.SHA256, 7, gpuhash.SHA1 | gpuhash.SHA256]
+    for trial in range(60):
+        L = int(rng.choice([1, 3, 16, 55, 56, 64, 100, 128, 1000, 4096, 16384, 65552, 100000]))
+        n = int(rng.integers(1, 70))
+        total = max(1, (n - 1) * L + int(rng.integers(1, L + 1)))
+        if total > 6 << 20:
+            continue
+        algos = int(rng.choice(masks))
+        data = oracle.gen(1000 + trial, int(rng.integers(0, 64)), total)
+        cuts = sorted(int(x) for x in rng.integers(0, total + 1, size=int(rng.integers(0, 6))))
+        spans, prev = [], 0
+        for c in cuts + [total]:
+            spans.append(data[prev:c])
+            prev = c
+        got = gh.HashParts(spans, L, algos)
+        for alg, _ in ALGS:
+            if algos & alg:
+                assert np.array_equal(got[alg], oracle.hash_msgs(alg, data, L, 2)), (trial, L, total, algos)

@@ -168,3 +168,37 @@ def test_c_example_verifies_a_torrent_on_disk(tmp_path):
     (tmp_path / "clip.mkv").write_bytes(bytes(bad))
     r = subprocess.run([exe, str(tor), str(tmp_path)], capture_output=True, text=True)
     assert r.returncode == 1 and "piece 5 failed" in r.stdout and "1 bad piece(s)" in r.stdout, r.stdout + r.stderr
+
+
+def test_parser_survives_mutated_torrents():
+    """Fuzz: single-byte mutations, truncations and random splices of a valid .torrent either parse
+    or are rejected with GH_EINVAL -- never crash, never hang (the parser faces bytes from peers)."""
+    rng = np.random.default_rng(99)
+    data = oracle.gen(5, 0, 70000).tobytes()
+    files = [(("a", "b.bin"), 30000), (("c.bin",), 40000)]
+    base = bytearray(benc({"announce": "x", "info": make_info("t", 16384, files, data), "z": [1, [2, {"k": b"v"}]]}))
+    ok = bad = 0
+    for trial in range(3000):
+        m = bytearray(base)
+        kind = trial % 4
+        if kind == 0:
+            m[int(rng.integers(0, len(m)))] = int(rng.integers(0, 256))
+        elif kind == 1:
+            m = m[: int(rng.integers(0, len(m)))]
+        elif kind == 2:
+            i, j = sorted(int(x) for x in rng.integers(0, len(m), size=2))
+            m = m[:i] + m[j:]
+        else:
+            i = int(rng.integers(0, len(m)))
+            m = m[:i] + bytes(rng.integers(0, 256, size=int(rng.integers(1, 12)), dtype=np.uint8)) + m[i:]
+        try:
+            mi = gpuhash.Metainfo(bytes(m))
+            assert mi.piece_length > 0 and len(mi.pieces) == 20 * mi.n_pieces
+            for path, n in mi.files:
+                assert ".." not in path.split("/") and not path.startswith("/") and n >= 0
+            mi.close()
+            ok += 1
+        except gpuhash.GpuHashError as e:
+            assert e.status == gpuhash.GH_EINVAL
+            bad += 1
+    assert ok > 0 and bad > 0
