@@ -366,6 +366,10 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 //   warp R  "rounds":   owns the chaining state, reads WK[t] and runs only the rounds;
 //   warp M  (fused MD5+SHA-256 only): MD5 over the same TMA tiles.
 // Hand-off is by mbarrier pairs (full/empty) on two WK buffers and on the TMA stages.
+#ifndef GH_HANDOFF
+#define GH_HANDOFF 4
+#endif
+constexpr int kHandoff = GH_HANDOFF;  // 64-byte blocks per S -> R hand-off (one barrier round trip each)
 constexpr int kSplitStages = 3;
 constexpr int kSplitTPS = 2;
 constexpr uint32_t kSplitChunk = kSplitTPS * kTileRowBytes;
@@ -377,7 +381,7 @@ struct SplitCfg {
 };
 template <int ALGO>
 __host__ __device__ constexpr int split_smem() {
-    return kSplitStages * kSplitTPS * kTileBytes + 2 * SplitCfg<ALGO>::kWkBytes + 128;
+    return kSplitStages * kSplitTPS * kTileBytes + 2 * kHandoff * SplitCfg<ALGO>::kWkBytes + 128;
 }
 
 __device__ __forceinline__ uint32_t sha1_k(int t) {
@@ -514,7 +518,7 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 
     const uint32_t tiles_u32 = smem_u32(smem);
     const uint32_t wk_u32 = tiles_u32 + kSplitStages * kSplitTPS * kTileBytes;
-    const uint32_t bars = wk_u32 + 2 * Cfg::kWkBytes;
+    const uint32_t bars = wk_u32 + 2 * kHandoff * Cfg::kWkBytes;
     const uint32_t tma_full = bars, tma_empty = bars + 8 * kSplitStages;
     const uint32_t w_full = bars + 16 * kSplitStages, w_empty = w_full + 16;
     constexpr uint32_t kTileReaders = WITH_MD5 ? 2 : 1;
@@ -566,11 +570,14 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
                 lds_block(row_base + (b * kSplitTPS + (j >> 1)) * kTileBytes, (j & 1u) * 4u, sw, r);
 #pragma unroll
                 for (int i = 0; i < 16; i++) w[i] = bswap(r[i]);
-                const uint32_t wb = jb & 1u, use = jb >> 1;
-                if (use) mbar_wait(w_empty + 8 * wb, (use - 1) & 1u);  // rounds warp has drained this buffer
-                expand_and_store<ALGO>(w, wk_u32 + wb * Cfg::kWkBytes + lane * 16);
-                __syncwarp();  // orders every lane's stores before lane 0's release-arrive
-                if (lane == 0) mbar_arrive1(w_full + 8 * wb);
+                const uint32_t pair = jb / kHandoff, half = jb % kHandoff;
+                const uint32_t wb = pair & 1u, use = pair >> 1;
+                if (half == 0 && use) mbar_wait(w_empty + 8 * wb, (use - 1) & 1u);  // rounds warp has drained this buffer
+                expand_and_store<ALGO>(w, wk_u32 + (wb * kHandoff + half) * Cfg::kWkBytes + lane * 16);
+                if (half == kHandoff - 1 || jb == n_blocks - 1) {
+                    __syncwarp();  // orders every lane's stores before lane 0's release-arrive
+                    if (lane == 0) mbar_arrive1(w_full + 8 * wb);
+                }
             }
             __syncwarp();
             if (lane == 0) {
@@ -588,13 +595,16 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
         if (job.prior == 0 || done_before) L.init();
         else L.load(job.state, job.n_msgs, m);
 #pragma unroll 1
-        for (uint32_t jb = 0; jb < n_blocks; jb++) {
-            const uint32_t wb = jb & 1u, use = jb >> 1;
+        for (uint32_t jb = 0; jb < n_blocks; jb += kHandoff) {
+            const uint32_t pair = jb / kHandoff, wb = pair & 1u, use = pair >> 1;
             mbar_wait(w_full + 8 * wb, use & 1u);
-            const uint32_t wk_addr = wk_u32 + wb * Cfg::kWkBytes + lane * 16;
-            if (jb < my_blocks) {
-                if constexpr (ALGO == GH_SHA1) sha1_rounds(L.s1, wk_addr, job.one);
-                else sha256_rounds(L.s2, wk_addr, job.one);
+#pragma unroll 1
+            for (uint32_t half = 0; half < kHandoff && jb + half < n_blocks; half++) {
+                const uint32_t wk_addr = wk_u32 + (wb * kHandoff + half) * Cfg::kWkBytes + lane * 16;
+                if (jb + half < my_blocks) {
+                    if constexpr (ALGO == GH_SHA1) sha1_rounds(L.s1, wk_addr, job.one);
+                    else sha256_rounds(L.s2, wk_addr, job.one);
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive1(w_empty + 8 * wb);
