@@ -532,3 +532,26 @@ def test_randomised_shapes_against_oracle(gh):
         for alg, _ in ALGS:
             if algos & alg:
                 assert np.array_equal(got[alg], oracle.hash_msgs(alg, data, L, 2)), (trial, L, total, algos)
+
+
+def test_concurrent_callers_share_one_context(gh):
+    """include/gpuhash.h promises that a gh_ctx may be used from several OS threads (calls are
+    serialised inside; goroutines migrate between threads): four threads, different inputs, at once."""
+    import threading
+    results, errors = {}, []
+
+    def work(i):
+        try:
+            L = [16384, 1000, 262144, 4096][i]
+            data = oracle.gen(200 + i, 0, 40 * L + i)
+            for _ in range(5):
+                got = gh.HashParts([data], L, gpuhash.SHA1 | gpuhash.MD5)
+            results[i] = (np.array_equal(got[gpuhash.SHA1], oracle.hash_msgs(oracle.SHA1, data, L)) and
+                          np.array_equal(got[gpuhash.MD5], oracle.hash_msgs(oracle.MD5, data, L)))
+        except Exception as e:  # noqa
+            errors.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors and results == {0: True, 1: True, 2: True, 3: True}
