@@ -3,7 +3,7 @@ sharded over 1/2/4/8 GPUs by ONE process (one gh_ctx over k devices, contiguous 
 ranges, no collective). Strong scaling of the end-to-end call on pinned host memory; every run is
 checked against expected digests (one injected fault). Writes gpurun_out/config4_multi.json."""
 import ctypes, json, os, sys, threading, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "downloader-go_b200")):
     sys.path.insert(0, p)
 import numpy as np

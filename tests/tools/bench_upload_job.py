@@ -1,7 +1,7 @@
 """An upload job of 24 files x 2 GiB, 64 MiB parts, MD5 + SHA-256 (what uploader.go:72-89 does file by
 file): one gh_hash_parts call per file vs ONE gh_hash_parts_per_file batch. Pinned host memory."""
 import ctypes, json, os, sys, threading, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "downloader-go_b200")):
     sys.path.insert(0, p)
 import numpy as np

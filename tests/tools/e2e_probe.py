@@ -1,7 +1,7 @@
 """e2e vs kernel time for long-message (chunk-interleaved) shapes; GPUHASH_NO_2D=1 switches the ring
 to per-row 1-D copies. Prints one JSON line."""
 import ctypes, json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "downloader-go_b200")):
     sys.path.insert(0, p)
 import numpy as np, torch

@@ -1,6 +1,6 @@
 """Config-5-like e2e: 10 000 pinned spans, 16 KiB pieces. Prints library wall / kernel time per call."""
 import ctypes, json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "downloader-go_b200")):
     sys.path.insert(0, p)
 import numpy as np, torch
