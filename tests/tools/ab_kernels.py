@@ -1,5 +1,5 @@
 """Kernel-only rates of the BASELINE config shapes for the current GPUHASH_* tuning switches.
-Usage: GPUHASH_FMA_ADDS=0|1 GPUHASH_TPS=2|4 python tools/ab_kernels.py  -> one JSON line."""
+Usage: GPUHASH_FMA_ADDS=0|1 GPUHASH_TPS=2|4 python tests/tools/ab_kernels.py  -> one JSON line."""
 import json
 import os
 import sys

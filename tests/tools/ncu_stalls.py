@@ -1,5 +1,5 @@
 """Summarise an ncu report's source page: stall reasons overall and for address ranges.
-Usage: python tools/ncu_stalls.py report.ncu-rep [top_n]"""
+Usage: python tests/tools/ncu_stalls.py report.ncu-rep [top_n]"""
 import csv
 import io
 import subprocess

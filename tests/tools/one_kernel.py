@@ -1,5 +1,5 @@
 """Runs one device-resident hashing launch a few times (for ncu captures).
-Usage: python tools/one_kernel.py <algos mask> <msg_len> <total_bytes>"""
+Usage: python tests/tools/one_kernel.py <algos mask> <msg_len> <total_bytes>"""
 import os
 import sys
 
