@@ -937,14 +937,20 @@ extern "C" int gh_hash_update_device_noalloc(int cuda_device, int algos, const v
         // kernel needs the address the symbol has on THIS device.
         std::lock_guard<std::mutex> g(g_noalloc_mu);
         if (!g_noalloc_ptr[cuda_device]) {
-            if (gh_kernels_init_device() != cudaSuccess) return GH_ECUDA;
+            if (gh_kernels_init_device() != cudaSuccess) {
+                cudaGetLastError();
+                return GH_ECUDA;
+            }
             void* p = nullptr;
             if (cudaGetSymbolAddress(&p, g_noalloc_state) != cudaSuccess || !p) {
                 cudaGetLastError();
                 return GH_ECUDA;
             }
             int n = 0;
-            if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, cuda_device) != cudaSuccess) return GH_ECUDA;
+            if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, cuda_device) != cudaSuccess) {
+                cudaGetLastError();
+                return GH_ECUDA;
+            }
             g_noalloc_sms[cuda_device] = n;
             g_noalloc_ptr[cuda_device] = static_cast<uint32_t*>(p);
         }
@@ -952,9 +958,20 @@ extern "C" int gh_hash_update_device_noalloc(int cuda_device, int algos, const v
         sms = g_noalloc_sms[cuda_device];
     }
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);  // null = the device's default stream
+    // On a failed launch: clear the runtime's error so the next CUDA call of this thread does not
+    // inherit it, and -- when the call owns the synchronisation (no caller stream) -- wait for what
+    // was already queued, so nothing of this call is still touching the caller's buffers on return.
+    auto failed = [&]() {
+        cudaGetLastError();
+        if (!cuda_stream) {
+            cudaStreamSynchronize(st);
+            cudaGetLastError();
+        }
+        return GH_ECUDA;
+    };
     if (prior_bytes == 0) {
         // A new batch starts: drop whatever the previous batch left in the part of the array this one uses.
-        if (cudaMemsetAsync(state, 0, n_msgs * GH_STATE_WORDS * sizeof(uint32_t), st) != cudaSuccess) return GH_ECUDA;
+        if (cudaMemsetAsync(state, 0, n_msgs * GH_STATE_WORDS * sizeof(uint32_t), st) != cudaSuccess) return failed();
     }
     GhJob j{};
     j.data = static_cast<const uint8_t*>(d_data);
@@ -969,9 +986,12 @@ extern "C" int gh_hash_update_device_noalloc(int cuda_device, int algos, const v
     j.md5 = d_md5;
     j.sha256 = d_sha256;
     if (algos & GH_SHA1)
-        if (gh_launch_hash(GH_SHA1, j, sms, st) != cudaSuccess) return GH_ECUDA;
+        if (gh_launch_hash(GH_SHA1, j, sms, st) != cudaSuccess) return failed();
     if (algos & (GH_MD5 | GH_SHA256))
-        if (gh_launch_hash(algos & (GH_MD5 | GH_SHA256), j, sms, st) != cudaSuccess) return GH_ECUDA;
-    if (!cuda_stream && cudaStreamSynchronize(st) != cudaSuccess) return GH_ECUDA;
+        if (gh_launch_hash(algos & (GH_MD5 | GH_SHA256), j, sms, st) != cudaSuccess) return failed();
+    if (!cuda_stream && cudaStreamSynchronize(st) != cudaSuccess) {
+        cudaGetLastError();
+        return GH_ECUDA;
+    }
     return GH_OK;
 }

@@ -218,9 +218,10 @@ int gh_hash_update_device(gh_ctx* ctx, int dev_index, int algos, const void* d_d
  * reference (which has no device code); it exists because of who calls this library. A download
  * worker sizes its payload buffers and staging ring to the HBM it has been given, so by the time a
  * job reaches hashing there may be nothing left for a midstate buffer and a cudaMalloc would fail
- * after the expensive part (the download) is already done. Other callers run where asking the CUDA
- * runtime for memory is off the table altogether: inside a host callback, or on a latency-sensitive
- * thread that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply.
+ * after the expensive part (the download) is already done. Other callers sit on a latency-sensitive
+ * thread that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply. (It still
+ * makes CUDA calls -- cudaSetDevice, a memset, kernel launches -- so it is not for places where no
+ * CUDA call is allowed at all, such as a cudaLaunchHostFunc callback.)
  *
  * Same arguments and results as gh_hash_update_device, except: there is no context (cuda_device is
  * a CUDA ordinal, made current by the call) and no d_state -- the midstates live in a fixed array

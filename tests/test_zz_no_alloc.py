@@ -44,6 +44,8 @@ def _run_batch(torch, ctx, seed, n, L, last, chunks, algos):
         return t[a].data_ptr() if algos & a else None
 
     for win, chunk, prior in _windows(torch, d, n, L, last, chunks):
+        # the window was filled on torch's stream; both hashers run on streams of their own
+        torch.cuda.synchronize()
         ctx.hash_update_device(algos, win.data_ptr(), chunk, chunk, prior, n, L, last, state.data_ptr(),
                                ptr(ref, gpuhash.SHA1), ptr(ref, gpuhash.MD5), ptr(ref, gpuhash.SHA256))
         gpuhash.hash_update_device_noalloc(0, algos, win.data_ptr(), chunk, chunk, prior, n, L, last,
