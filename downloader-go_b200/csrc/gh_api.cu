@@ -10,6 +10,7 @@
 // thread pool. Pieces / parts are independent, so devices get contiguous 64-aligned message ranges and
 // there is no collective of any kind.
 #include <cuda_runtime.h>
+#include <errno.h>
 #include <fcntl.h>
 #include <unistd.h>
 
@@ -110,36 +111,41 @@ class Pool {
         std::unique_lock<std::mutex> lk(dmu);
         dcv.wait(lk, [&] { return pending.load() == 0; });
     }
-    // pread of [off, off+n) into dst, in 4 MiB pieces over the pool; bytes the file does not have
-    // (missing or short file) read as zeros, so the pieces that touch them simply fail verification.
-    void read(int fd, uint64_t off, uint8_t* dst, uint64_t n) {
-        const uint64_t grain = 4ull << 20;
-        parallel_for((n + grain - 1) / grain, [&](uint64_t i) {
-            uint64_t o = i * grain, len = std::min(grain, n - o);
-            uint8_t* p = dst + o;
-            while (len) {
-                const ssize_t r = fd >= 0 ? pread(fd, p, len, static_cast<off_t>(off + o)) : 0;
-                if (r <= 0) {
-                    memset(p, 0, len);
-                    break;
-                }
-                p += r; o += r; len -= r;
+    // pread of [off, off+n) into dst, in 4 MiB pieces over the pool. Bytes the file does not have
+    // (fd < 0: file missing; or a short file) read as zeros, so the pieces that touch them simply fail
+    // verification. A read ERROR is something else: the first errno is returned (0 = fine).
+    static int pread_full(int fd, uint64_t off, uint8_t* p, uint64_t len) {
+        while (len) {
+            const ssize_t r = fd >= 0 ? pread(fd, p, len, static_cast<off_t>(off)) : 0;
+            if (r < 0) {
+                if (errno == EINTR) continue;
+                return errno;
             }
-        });
+            if (r == 0) {
+                memset(p, 0, len);
+                break;
+            }
+            p += r; off += r; len -= r;
+        }
+        return 0;
     }
-    void read2d(int fd, uint64_t off, uint64_t spitch, uint8_t* dst, uint64_t dpitch, uint64_t width, uint64_t rows) {
-        parallel_for(rows, [&](uint64_t r) {
-            uint64_t o = off + r * spitch, len = width;
-            uint8_t* p = dst + r * dpitch;
-            while (len) {
-                const ssize_t k = fd >= 0 ? pread(fd, p, len, static_cast<off_t>(o)) : 0;
-                if (k <= 0) {
-                    memset(p, 0, len);
-                    break;
-                }
-                p += k; o += k; len -= k;
-            }
+    int read(int fd, uint64_t off, uint8_t* dst, uint64_t n) {
+        const uint64_t grain = 4ull << 20;
+        std::atomic<int> err{0};
+        parallel_for((n + grain - 1) / grain, [&](uint64_t i) {
+            const uint64_t o = i * grain, len = std::min(grain, n - o);
+            const int e = pread_full(fd, off + o, dst + o, len);
+            if (e) err.store(e);
         });
+        return err.load();
+    }
+    int read2d(int fd, uint64_t off, uint64_t spitch, uint8_t* dst, uint64_t dpitch, uint64_t width, uint64_t rows) {
+        std::atomic<int> err{0};
+        parallel_for(rows, [&](uint64_t r) {
+            const int e = pread_full(fd, off + r * spitch, dst + r * dpitch, width);
+            if (e) err.store(e);
+        });
+        return err.load();
     }
 
     // strided copy: rows of `width` bytes, pitches in bytes; rows are spread over the pool.
@@ -227,27 +233,42 @@ struct gh_ctx {
     std::string last_error;
     gh_stats stats{};
     std::atomic<uint64_t> launches{0}, h2d{0}, d2h{0};
-    bool lost = false;
+    std::atomic<bool> lost{false};
     bool stream_open = false;  // a gh_stream owns the ring until it is finished or aborted
+    std::mutex err_mu;         // last_error is written by one host thread per device
+    std::atomic<int64_t> fail_copy_in{-1};  // gh_debug_fail_nth_copy: >= 0 = payload copies left before a forced failure
 };
 
 namespace {
 
 int fail(gh_ctx* c, int code, const std::string& msg) {
-    if (c) c->last_error = msg;
+    if (c) {
+        std::lock_guard<std::mutex> g(c->err_mu);
+        c->last_error = msg;
+    }
     return code;
 }
 
 int cuda_fail(gh_ctx* c, cudaError_t e, const char* what) {
     std::string msg = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    cudaGetLastError();  // the error is reported through the status; do not leave it for the caller's next CUDA call
+    bool lost = false;
     if (c) {
-        c->last_error = msg;
         if (e == cudaErrorIllegalAddress || e == cudaErrorLaunchFailure || e == cudaErrorHardwareStackError ||
             e == cudaErrorIllegalInstruction || e == cudaErrorMisalignedAddress)
             c->lost = true;
+        lost = c->lost;
+        std::lock_guard<std::mutex> g(c->err_mu);
+        c->last_error = msg;
     }
     if (e == cudaErrorMemoryAllocation) return GH_ENOMEM;
-    return (c && c->lost) ? GH_ECTX_LOST : GH_ECUDA;
+    return lost ? GH_ECTX_LOST : GH_ECUDA;
+}
+
+// Payload copies go through here so that tests can make the n-th one fail (gh_debug_fail_nth_copy).
+cudaError_t payload_copy_gate(gh_ctx* c) {
+    if (c->fail_copy_in.load(std::memory_order_relaxed) < 0) return cudaSuccess;
+    return c->fail_copy_in.fetch_sub(1) == 0 ? cudaErrorUnknown : cudaSuccess;
 }
 
 #define GH_CUDA(ctx, call)                                           \
@@ -328,16 +349,78 @@ int launch_window(gh_ctx* c, Device& d, int algos, GhJob job, cudaStream_t strea
 struct SpanIndex {
     size_t n = 0;
     std::vector<const uint8_t*> ptr;  // null for file-backed runs
-    std::vector<int> fd;              // -1 for memory runs and for files that could not be opened
+    std::vector<const char*> path;    // file-backed runs: the caller's path (valid for the duration of the call)
     std::vector<char> is_file;
     std::vector<uint64_t> start;      // stream offset of each run, plus the total at [n]
     std::vector<char> pinned;
     uint64_t total() const { return start[n]; }
-    ~SpanIndex() {
-        for (size_t i = 0; i < fd.size(); i++)
-            if (fd[i] >= 0) close(fd[i]);
+};
+
+// Files are opened when a window first needs them and at most kMaxOpen stay open per device thread:
+// a torrent of 10 000 files (BASELINE config 5) must not run into RLIMIT_NOFILE. A file that does not
+// exist is a hole (fd -1: its bytes read as zeros and the pieces over it fail verification); any
+// other failure to open -- EMFILE, EACCES, EIO ... -- is an error of the call, reported with errno.
+class FdCache {
+   public:
+    static constexpr size_t kMaxOpen = 64;
+    ~FdCache() {
+        for (auto& e : open_)
+            if (e.fd >= 0) close(e.fd);
+    }
+    // 0 = ok (*fd may be -1 for a missing file), else errno
+    int get(const SpanIndex& ix, size_t i, int* fd) {
+        for (auto& e : open_)
+            if (e.idx == i) {
+                e.stamp = ++clock_;
+                *fd = e.fd;
+                return 0;
+            }
+        int f = -1;
+        if (ix.path[i]) {
+            do f = open(ix.path[i], O_RDONLY | O_CLOEXEC);
+            while (f < 0 && errno == EINTR);
+            if (f < 0 && errno != ENOENT && errno != ENOTDIR) return errno;
+        }
+        if (open_.size() >= kMaxOpen) {
+            size_t victim = 0;
+            for (size_t k = 1; k < open_.size(); k++)
+                if (open_[k].stamp < open_[victim].stamp) victim = k;
+            if (open_[victim].fd >= 0) close(open_[victim].fd);
+            open_[victim] = open_.back();
+            open_.pop_back();
+        }
+        open_.push_back({i, f, ++clock_});
+        *fd = f;
+        return 0;
+    }
+
+   private:
+    struct Entry { size_t idx; int fd; uint64_t stamp; };
+    std::vector<Entry> open_;
+    uint64_t clock_ = 0;
+};
+
+// Byte ranges of a slot's pinned mirror that were filled by the host and still need their H2D copy.
+// Kept as separate runs: a pinned span DMA'd straight into the slot may sit between two staged ones,
+// and one copy over the hull would overwrite it with whatever the mirror held there.
+struct StagedRuns {
+    struct Run { uint64_t off, width, rows, pitch; };  // rows of `width` bytes, `pitch` apart (rows == 1: plain range)
+    std::vector<Run> runs;
+    void add(uint64_t lo, uint64_t hi) {
+        if (lo >= hi) return;
+        if (!runs.empty() && runs.back().rows == 1 && runs.back().off + runs.back().width == lo) runs.back().width = hi - runs.back().off;
+        else runs.push_back({lo, hi - lo, 1, 0});
+    }
+    void add_rows(uint64_t off, uint64_t pitch, uint64_t width, uint64_t rows) {
+        if (!width || !rows) return;
+        if (width == pitch || rows == 1) add(off, off + (rows - 1) * pitch + width);
+        else runs.push_back({off, width, rows, pitch});
     }
 };
+
+int io_fail(gh_ctx* c, int err, const char* path) {
+    return fail(c, GH_EIO, std::string("reading ") + (path ? path : "?") + ": " + strerror(err));
+}
 
 // [lo, hi) of the pinned allocation that contains p, or false. cudaPointerGetAttributes costs a few
 // microseconds; with thousands of spans cut from a few pinned buffers (10 000 small files) asking once
@@ -407,14 +490,14 @@ void build_index(const gh_span* spans, size_t n, SpanIndex* ix, bool merge = tru
     }
     ix->n = ix->ptr.size();
     ix->start.push_back(off);
-    ix->fd.assign(ix->n, -1);
+    ix->path.assign(ix->n, nullptr);
     ix->is_file.assign(ix->n, 0);
 }
 
 void build_index_files(const gh_file* files, size_t n, SpanIndex* ix) {
     ix->n = n;
     ix->ptr.assign(n, nullptr);
-    ix->fd.assign(n, -1);
+    ix->path.assign(n, nullptr);
     ix->is_file.assign(n, 1);
     ix->start.resize(n + 1);
     ix->pinned.assign(n, 0);
@@ -422,16 +505,16 @@ void build_index_files(const gh_file* files, size_t n, SpanIndex* ix) {
     for (size_t i = 0; i < n; i++) {
         ix->start[i] = off;
         off += files[i].len;
-        if (files[i].len && files[i].path) ix->fd[i] = open(files[i].path, O_RDONLY | O_CLOEXEC);
+        if (files[i].len) ix->path[i] = files[i].path;
     }
     ix->start[n] = off;
 }
 
 // Copies stream bytes [a, b) into slot memory at d_dst (device) / h_dst (pinned mirror, same offset).
-// Pinned spans are DMA'd directly; pageable ones are staged. `staged_lo/hi` accumulate the range of
-// the mirror that needs one H2D afterwards.
-int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint64_t dst_off, uint64_t* staged_lo,
-           uint64_t* staged_hi) {
+// Pinned spans are DMA'd directly; pageable and file-backed ones are staged in the mirror, and
+// `staged` collects the mirror ranges that need their H2D afterwards (flush_staged).
+int gather(gh_ctx* c, const SpanIndex& ix, FdCache& fds, uint64_t a, uint64_t b, Slot& s, uint64_t dst_off,
+           StagedRuns* staged) {
     if (a >= b) return GH_OK;
     size_t i = std::upper_bound(ix.start.begin(), ix.start.begin() + ix.n, a) - ix.start.begin() - 1;
     uint64_t x = a;
@@ -439,21 +522,25 @@ int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint
         const uint64_t s_lo = ix.start[i], s_hi = ix.start[i + 1];
         if (s_hi <= x) { i++; continue; }
         const uint64_t hi = std::min(b, s_hi);
-        const uint8_t* src = ix.ptr[i] + (x - s_lo);
         const uint64_t len = hi - x;
         const uint64_t doff = dst_off + (x - a);
+        GH_CUDA(c, payload_copy_gate(c));
         if (ix.pinned[i]) {
-            GH_CUDA(c, cudaMemcpyAsync(s.d_buf + doff, src, len, cudaMemcpyHostToDevice, s.stream));
+            GH_CUDA(c, cudaMemcpyAsync(s.d_buf + doff, ix.ptr[i] + (x - s_lo), len, cudaMemcpyHostToDevice, s.stream));
         } else {
             if (!s.h_pin) GH_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256));
             if (s.h2d_pending) {  // the previous window's DMA out of this mirror must have drained
                 GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
                 s.h2d_pending = false;
             }
-            if (ix.is_file[i]) c->pool->read(ix.fd[i], x - s_lo, s.h_pin + doff, len);
-            else c->pool->copy(s.h_pin + doff, src, len);
-            *staged_lo = std::min(*staged_lo, doff);
-            *staged_hi = std::max(*staged_hi, doff + len);
+            if (ix.is_file[i]) {
+                int fd = -1, err = fds.get(ix, i, &fd);
+                if (!err) err = c->pool->read(fd, x - s_lo, s.h_pin + doff, len);
+                if (err) return io_fail(c, err, ix.path[i]);
+            } else {
+                c->pool->copy(s.h_pin + doff, ix.ptr[i] + (x - s_lo), len);
+            }
+            staged->add(doff, doff + len);
         }
         c->h2d += len;
         x = hi;
@@ -462,10 +549,15 @@ int gather(gh_ctx* c, const SpanIndex& ix, uint64_t a, uint64_t b, Slot& s, uint
     return GH_OK;
 }
 
-int flush_staged(gh_ctx* c, Slot& s, uint64_t lo, uint64_t hi) {
-    if (lo >= hi) return GH_OK;
-    GH_CUDA(c, cudaMemcpyAsync(s.d_buf + lo, s.h_pin + lo, hi - lo, cudaMemcpyHostToDevice, s.stream));
-    s.h2d_pending = true;
+int flush_staged(gh_ctx* c, Slot& s, const StagedRuns& staged) {
+    for (const auto& r : staged.runs) {
+        if (r.rows == 1)
+            GH_CUDA(c, cudaMemcpyAsync(s.d_buf + r.off, s.h_pin + r.off, r.width, cudaMemcpyHostToDevice, s.stream));
+        else
+            GH_CUDA(c, cudaMemcpy2DAsync(s.d_buf + r.off, r.pitch, s.h_pin + r.off, r.pitch, r.width, r.rows,
+                                         cudaMemcpyHostToDevice, s.stream));
+        s.h2d_pending = true;
+    }
     return GH_OK;
 }
 
@@ -494,9 +586,9 @@ struct MsgTable {
 // [(g0+m)*L + prior, +min(chunk, len_m - prior)) to slot offset m*chunk. Consecutive rows that lie
 // inside one span move as one strided copy (DMA for pinned spans, pooled memcpy for pageable ones);
 // a row that straddles a span (file) boundary falls back to the byte-exact 1-D gather.
-int gather_rows(gh_ctx* c, const SpanIndex& ix, const MsgTable& T, Slot& s, uint64_t g0, uint64_t g, uint64_t prior,
-                uint64_t chunk) {
-    uint64_t st_lo = ~0ull, st_hi = 0;
+int gather_rows(gh_ctx* c, const SpanIndex& ix, FdCache& fds, const MsgTable& T, Slot& s, uint64_t g0, uint64_t g,
+                uint64_t prior, uint64_t chunk) {
+    StagedRuns staged;
     size_t si = 0;
     uint64_t m = 0;
     const uint64_t L = T.L;
@@ -509,7 +601,7 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, const MsgTable& T, Slot& s, uint
         while (si > 0 && ix.start[si] > lo) si--;
         const bool inside = si < ix.n && ix.start[si] <= lo && lo + w <= ix.start[si + 1];
         if (!inside) {
-            int rc = gather(c, ix, lo, lo + w, s, m * chunk, &st_lo, &st_hi);
+            int rc = gather(c, ix, fds, lo, lo + w, s, m * chunk, &staged);
             if (rc) return rc;
             m++;
             continue;
@@ -524,8 +616,9 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, const MsgTable& T, Slot& s, uint
             if (T.off(m2) + prior + w > ix.start[si + 1]) break;
             rows++;
         }
-        const uint8_t* src = ix.ptr[si] + (lo - ix.start[si]);
+        GH_CUDA(c, payload_copy_gate(c));
         if (ix.pinned[si]) {
+            const uint8_t* src = ix.ptr[si] + (lo - ix.start[si]);
             static const bool no2d = getenv("GPUHASH_NO_2D") != nullptr;
             if (no2d) {
                 for (uint64_t r = 0; r < rows; r++)
@@ -539,15 +632,19 @@ int gather_rows(gh_ctx* c, const SpanIndex& ix, const MsgTable& T, Slot& s, uint
                 GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
                 s.h2d_pending = false;
             }
-            if (ix.is_file[si]) c->pool->read2d(ix.fd[si], lo - ix.start[si], L, s.h_pin + m * chunk, chunk, w, rows);
-            else c->pool->copy2d(s.h_pin + m * chunk, chunk, src, L, w, rows);
-            st_lo = std::min(st_lo, m * chunk);
-            st_hi = std::max(st_hi, (m + rows - 1) * chunk + w);
+            if (ix.is_file[si]) {
+                int fd = -1, err = fds.get(ix, si, &fd);
+                if (!err) err = c->pool->read2d(fd, lo - ix.start[si], L, s.h_pin + m * chunk, chunk, w, rows);
+                if (err) return io_fail(c, err, ix.path[si]);
+            } else {
+                c->pool->copy2d(s.h_pin + m * chunk, chunk, ix.ptr[si] + (lo - ix.start[si]), L, w, rows);
+            }
+            staged.add_rows(m * chunk, chunk, w, rows);
         }
         c->h2d += w * rows;
         m += rows;
     }
-    return flush_staged(c, s, st_lo, st_hi);
+    return flush_staged(c, s, staged);
 }
 
 int slot_launch(gh_ctx* c, Device& d, Slot& s, int algos, const GhJob& j) {
@@ -572,10 +669,38 @@ struct BatchArgs {
     uint64_t n_total;
 };
 
+// Leaves the device idle and the ring in its initial state: every queued copy and kernel of this
+// context has finished, no slot is marked busy. Called on every error exit, so that (a) a one-shot
+// call never returns while a DMA may still read the caller's buffers -- the promise the header makes
+// for all exits, not only the successful one -- and (b) the next call cannot overwrite a slot that a
+// stale kernel is still reading.
+void drain_device(Device& d) {
+    if (cudaSetDevice(d.ordinal) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    for (auto& s : d.slots) {
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        s.in_use = false;
+        s.h2d_pending = false;
+    }
+    if (d.stream) cudaStreamSynchronize(d.stream);
+    cudaGetLastError();
+}
+
+int run_device_body(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m1, double* kernel_ms);
+
 int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m1, double* kernel_ms) {
     *kernel_ms = 0;
     if (m0 >= m1) return GH_OK;
+    const int rc = run_device_body(c, d, A, m0, m1, kernel_ms);
+    if (rc != GH_OK) drain_device(d);
+    return rc;
+}
+
+int run_device_body(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m1, double* kernel_ms) {
     GH_CUDA(c, cudaSetDevice(d.ordinal));
+    FdCache fds;
     const MsgTable& T = *A.T;
     const uint64_t n = m1 - m0, L = A.msg_len;
     const bool table = !T.uniform();
@@ -618,18 +743,18 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
         for (uint64_t q = m0; q < m1; q += per, b++) {
             Slot& s = d.slots[b % d.slots.size()];
             const uint64_t k = std::min(per, m1 - q);
-            uint64_t st_lo = ~0ull, st_hi = 0;
+            StagedRuns staged;
             if ((rc = slot_begin(c, s))) return rc;
             // runs of messages that follow each other in the stream at full length land back to back
             // in the slot as well: one gather per run (the whole window in the uniform case)
             for (uint64_t r0 = q; r0 < q + k;) {
                 uint64_t r1 = r0 + 1;
                 while (r1 < q + k && T.len(r1 - 1) == L && T.off(r1) == T.off(r1 - 1) + L) r1++;
-                if ((rc = gather(c, *A.ix, T.off(r0), T.off(r1 - 1) + T.len(r1 - 1), s, (r0 - q) * L, &st_lo, &st_hi)))
+                if ((rc = gather(c, *A.ix, fds, T.off(r0), T.off(r1 - 1) + T.len(r1 - 1), s, (r0 - q) * L, &staged)))
                     return rc;
                 r0 = r1;
             }
-            if ((rc = flush_staged(c, s, st_lo, st_hi))) return rc;
+            if ((rc = flush_staged(c, s, staged))) return rc;
             GhJob j = job;
             j.data = s.d_buf;
             j.stride = L;
@@ -664,7 +789,7 @@ int run_device(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint64_t m
             for (uint64_t prior = 0; prior < L; prior += chunk, b++) {
                 Slot& s = d.slots[b % d.slots.size()];
                 if ((rc = slot_begin(c, s))) return rc;
-                if ((rc = gather_rows(c, *A.ix, T, s, g0, g, prior, chunk))) return rc;
+                if ((rc = gather_rows(c, *A.ix, fds, T, s, g0, g, prior, chunk))) return rc;
                 GhJob j = job;
                 j.data = s.d_buf;
                 j.stride = chunk;
@@ -840,11 +965,24 @@ const char* gh_strerror(int status) {
         case GH_ECUDA: return "CUDA error";
         case GH_ECTX_LOST: return "context lost after a device fault";
         case GH_ERANGE: return "size beyond limit";
+        case GH_EIO: return "file could not be opened or read";
         default: return "unknown status";
     }
 }
 
-const char* gh_last_error(gh_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+const char* gh_last_error(gh_ctx* ctx) {
+    if (!ctx) return "";
+    static thread_local std::string copy;  // valid until this thread's next gh_last_error call
+    std::lock_guard<std::mutex> g(ctx->err_mu);
+    copy = ctx->last_error;
+    return copy.c_str();
+}
+
+int gh_debug_fail_nth_copy(gh_ctx* ctx, int64_t n) {
+    if (!ctx) return GH_EINVAL;
+    ctx->fail_copy_in.store(n);
+    return GH_OK;
+}
 
 void gh_shard_range(uint64_t n_msgs, int n_shards, int shard, uint64_t* begin, uint64_t* end) {
     if (n_shards < 1) n_shards = 1;
@@ -1096,9 +1234,18 @@ int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
     Device& d = c->devs[0];
     GH_CUDA(c, cudaSetDevice(d.ordinal));
     Slot& s = d.slots[st->window % d.slots.size()];
-    int rc;
-    if ((rc = slot_begin(c, s))) return rc;
-    if ((rc = flush_staged(c, s, 0, n_bytes))) return rc;
+    int rc = slot_begin(c, s);
+    StagedRuns staged;
+    staged.add(0, n_bytes);
+    if (!rc) {
+        const cudaError_t ge = payload_copy_gate(c);
+        if (ge != cudaSuccess) rc = cuda_fail(c, ge, "gh_stream_submit: copy");
+    }
+    if (!rc) rc = flush_staged(c, s, staged);
+    if (rc) {  // nothing of this stream may still be running when the caller sees the error and aborts
+        drain_device(d);
+        return rc;
+    }
     c->h2d += n_bytes;
     const uint64_t k = std::min(st->per, st->n - st->next_msg);
     GhJob j{};
@@ -1117,7 +1264,10 @@ int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
         j.ok_words = d.d_ok;
         j.ok_base = rel;
     }
-    if ((rc = slot_launch(c, d, s, st->algos, j))) return rc;
+    if ((rc = slot_launch(c, d, s, st->algos, j))) {
+        drain_device(d);
+        return rc;
+    }
     st->next_msg += k;
     st->fed += n_bytes;
     st->window++;

@@ -32,6 +32,7 @@ struct GhJob {
     uint64_t first_msg;
     uint64_t count;
     uint32_t tma_inner;
+    uint32_t chains_per_cta;  // trio kernel only: chains (message-warps) per CTA, 1..3
     uint32_t one;  // always 1; a kernel parameter so that ptxas keeps x*one+y as an IMAD (gh_hash.cuh addf)
 };
 

@@ -22,6 +22,9 @@
 
 #include <cuda.h>
 #include <stdlib.h>
+
+#include <algorithm>
+#include <string>
 #include <string.h>
 
 #include "../../include/gpuhash.h"
@@ -369,6 +372,12 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 #ifndef GH_HANDOFF
 #define GH_HANDOFF 4
 #endif
+#ifndef GH_R_IADD3
+#define GH_R_IADD3 1  // SHA-1 rounds warps: f + e + WK as one IADD3 (see sha1_rounds); 0 = the two-IMAD form
+#endif
+#ifndef GH_TRIO_R_LOW
+#define GH_TRIO_R_LOW 0  // 1 = rounds warps take the low warp ids of their sub-partition (A/B of the issue arbiter's preference)
+#endif
 constexpr int kHandoff = GH_HANDOFF;  // 64-byte blocks per S -> R hand-off (one barrier round trip each)
 constexpr int kSplitStages = 3;
 constexpr int kSplitTPS = 2;
@@ -422,8 +431,15 @@ __device__ __forceinline__ void sha1_rounds(uint32_t (&s)[5], uint32_t wk_addr, 
             else if (t < 40) f = f_xor3(b, c, d);
             else if (t < 60) f = f_maj(b, c, d);
             else f = f_xor3(b, c, d);
+#if GH_R_IADD3
+            // f + e + WK as ONE three-input add on the ALU pipe: a fourth ALU instruction per round, but no
+            // cross-pipe hop on the path a[t] -> f -> sum -> a[t+2] (static schedule 682 vs 749 clocks per block)
+            const uint32_t pre = e + wk[i];
+            const uint32_t tmp = rotl(a, 5) + (f + pre);
+#else
             const uint32_t pre = addf<true>(e, wk[i], one);
             const uint32_t tmp = rotl(a, 5) + (f + pre);
+#endif
             e = d; d = c; c = rotl(b, 30); b = a; a = tmp;
         }
     }
@@ -659,6 +675,188 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     }
 }
 
+// ---------------------------------------------------------------------------- trio hasher (SHA-1)
+// What the two kernels above leave on the table (measured on B200, profiles/r02_ab_team_trio.jsonl):
+// a warp that is alone on its sub-partition issues at ~0.6 IPC whatever it runs -- its own dependent
+// instructions are 4-5 clocks apart and nothing fills the gaps -- so neither the lane kernel (one
+// chain = one warp = 1 190 clk per 64-byte block at config 2) nor a rounds-warp fed by ONE schedule
+// warp (the schedule warp, alone on its sub-partition, needs ~490 clk per block and becomes the
+// bottleneck as soon as it serves more than one chain) gets near the ALU pipes' capacity. The pipes
+// only fill when every sub-partition holds two or three warps with independent work.
+//
+// The schedule of block b does not depend on block b-1, so one chain can feed on SEVERAL schedule
+// warps. Here a chain (32 messages) is served by three warps:
+//   R    rounds: owns the chaining state, reads W+K from shared memory, runs only the 80 rounds;
+//   S_a  schedule of the even hand-off batches (TMA tiles -> byte swap -> W[0..79] + K -> shared memory);
+//   S_b  schedule of the odd ones.
+// and a CTA carries up to three chains: nine working warps on the four sub-partitions of one SM. With
+// warp w on sub-partition w % 4 the roles are laid out so that sub-partitions 0-2 each hold one R and
+// one S warp (R has the higher warp id: the issue arbiter prefers it, and R is the serial chain) and
+// sub-partition 3 holds the three remaining S warps: ~486 + 232 ALU-pipe issue clocks per block on
+// 0-2, 3 x 232 on 3 -- the same ~710 everywhere, against 944 for one whole block on one pipe.
+// Every (chain, buffer) has exactly one producer warp and one consumer warp, so the full/empty
+// mbarrier pairs never have two waiters a phase apart; each S warp owns the two TMA stages of its
+// batch parity and is their only reader, so the tile ring needs no "empty" barrier.
+#ifndef GH_TRIO_DEBUG
+#define GH_TRIO_DEBUG 0  // measurement builds only: 1 = rounds warps idle, 2 = schedule warps idle (digests are then wrong)
+#endif
+constexpr int kTrioMaxChains = 3;
+constexpr int kTrioH = 2;          // blocks per hand-off batch = one TMA tile row of 128 bytes per message
+constexpr int kTrioStages = 4;     // per chain: two per schedule warp
+constexpr uint32_t kTrioWkBlock = 80 * 32 * 4;                       // [t/4][lane][4]
+constexpr uint32_t kTrioTilesPerChain = kTrioStages * kTileBytes;    // 16 KiB
+constexpr uint32_t kTrioWkPerChain = 2 * kTrioH * kTrioWkBlock;      // 40 KiB: one buffer per schedule warp
+constexpr uint32_t kTrioBarsPerChain = 8 * (kTrioStages + 4);
+__host__ __device__ constexpr uint32_t trio_smem(int chains) {
+    return chains * (kTrioTilesPerChain + kTrioWkPerChain + kTrioBarsPerChain) + 64;
+}
+__host__ __device__ constexpr int trio_warps(int chains) { return chains == 1 ? 3 : chains == 2 ? 8 : 12; }
+
+// role of warp w in a CTA of `chains` chains: 0 = rounds, 1 = schedule (even batches), 2 = schedule (odd), 3 = none
+__device__ __forceinline__ void trio_role(uint32_t w, uint32_t chains, uint32_t* role, uint32_t* chain) {
+    *role = 3;
+    *chain = 0;
+    if (chains == 1) {  // three warps, three sub-partitions
+        *role = w;
+    } else if (chains == 2) {  // R0 R1 on 0,1 with S_b of the same chain below them; S_a on 2,3
+        if (w == 4 || w == 5) { *role = 0; *chain = w - 4; }
+        else if (w == 0 || w == 1) { *role = 2; *chain = w; }
+        else if (w == 2 || w == 3) { *role = 1; *chain = w - 2; }
+        else if (w == 6 || w == 7) { *role = 3; }
+    } else {
+#if GH_TRIO_R_LOW
+        if (w <= 2) { *role = 0; *chain = w; }
+        else if (w >= 4 && w <= 6) { *role = 2; *chain = w - 4; }
+#else
+        if (w >= 4 && w <= 6) { *role = 0; *chain = w - 4; }
+        else if (w <= 2) { *role = 2; *chain = w; }
+#endif
+        else if ((w & 3u) == 3u) { *role = 1; *chain = w >> 2; }
+    }
+}
+
+__global__ void __launch_bounds__(32 * 12)
+gh_hash_trio(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t chains = job.chains_per_cta;
+    uint32_t role, ci;
+    trio_role(threadIdx.x >> 5, chains, &role, &ci);
+    const uint64_t mw0 = static_cast<uint64_t>(blockIdx.x) * chains;  // first message-warp (chain) of this CTA
+    const uint64_t n_mw_total = (job.count + 31) / 32;
+    const uint32_t n_mw = static_cast<uint32_t>(n_mw_total - mw0 < chains ? n_mw_total - mw0 : chains);
+
+    // As in gh_hash_split: every message of the grid has the same number of bytes in this launch.
+    const uint64_t common_remain = job.prior >= job.msg_len ? 0 : job.msg_len - job.prior;
+    const uint32_t n_blocks = static_cast<uint32_t>((common_remain < job.chunk_len ? common_remain : job.chunk_len) >> 6);
+    const uint32_t n_batches = (n_blocks + kTrioH - 1) / kTrioH;
+
+    // shared memory: [tiles of chain 0..][WK of chain 0..][barriers of chain 0..]
+    const uint32_t base = smem_u32(smem);
+    const uint32_t tiles = base + ci * kTrioTilesPerChain;
+    const uint32_t wk = base + chains * kTrioTilesPerChain + ci * kTrioWkPerChain;
+    const uint32_t bars = base + chains * (kTrioTilesPerChain + kTrioWkPerChain) + ci * kTrioBarsPerChain;
+    const uint32_t tile_full = bars, w_full = bars + 8 * kTrioStages, w_empty = w_full + 16;
+    if (threadIdx.x == 0) {
+        const uint32_t b0 = base + chains * (kTrioTilesPerChain + kTrioWkPerChain);
+        for (uint32_t k = 0; k < chains * (kTrioStages + 4); k++) mbar_init(b0 + 8 * k, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();  // the only CTA-wide barrier
+    if (role == 3 || ci >= n_mw) return;
+
+    if (role != 0) {
+        // ------------------------------------------------------------------ schedule warp of parity p
+        const uint32_t p = role - 1;  // batches q = p, p+2, p+4 ...; WK buffer p; TMA stages p and p+2
+        const uint32_t sw = lane & 7u;
+        const uint32_t row0 = static_cast<uint32_t>(job.first_msg + (mw0 + ci) * 32u);
+        const uint32_t row_base = tiles + lane * kTileRowBytes;
+        const uint32_t wk0 = wk + p * kTrioH * kTrioWkBlock + lane * 16;
+        auto issue = [&](uint32_t q) {  // batch q = bytes [128 q, 128 q + 128) of every message
+            const uint32_t st = q % kTrioStages;
+            mbar_arrive_expect_tx(tile_full + 8 * st, kTileBytes);
+            tma_load_box(tiles + st * kTileBytes, &tmap, q * (kTileRowBytes / 4), row0, tile_full + 8 * st);
+        };
+        if (lane == 0) {
+            if (p < n_batches) issue(p);
+            if (p + 2 < n_batches) issue(p + 2);
+        }
+        uint32_t use = 0;
+#pragma unroll 1
+        for (uint32_t q = p; q < n_batches; q += 2, use++) {
+            const uint32_t st = q % kTrioStages;
+            mbar_wait(tile_full + 8 * st, (q / kTrioStages) & 1u);
+            if (use) mbar_wait(w_empty + 8 * p, (use - 1) & 1u);  // R has drained this warp's buffer
+            const uint32_t nb = min(static_cast<uint32_t>(kTrioH), n_blocks - q * kTrioH);
+#pragma unroll 1
+            for (uint32_t j = 0; j < nb; j++) {
+#if GH_TRIO_DEBUG != 2
+                uint32_t r[16], w[16];
+                lds_block(row_base + st * kTileBytes, j * 4u, sw, r);
+#pragma unroll
+                for (int k = 0; k < 16; k++) w[k] = bswap(r[k]);
+                expand_and_store<GH_SHA1>(w, wk0 + j * kTrioWkBlock);
+#endif
+            }
+            __syncwarp();  // every lane's stores and tile reads precede lane 0's release-arrive / re-issue
+            if (lane == 0) {
+                mbar_arrive1(w_full + 8 * p);
+                if (q + kTrioStages < n_batches) issue(q + kTrioStages);
+            }
+        }
+        return;
+    }
+
+    // ---------------------------------------------------------------------- rounds warp
+    const uint64_t m = job.first_msg + (mw0 + ci) * 32u + lane;
+    const bool active = m < job.first_msg + job.count;
+    const uint64_t total_m = !active ? 0 : job.lens ? job.lens[m] : (m == job.n_msgs - 1 ? job.last_msg_len : job.msg_len);
+    const bool done_before = !active || (job.prior > 0 && job.prior >= total_m);
+    const uint64_t remain = done_before ? 0 : total_m - job.prior;
+    const bool ends_now = !done_before && remain <= job.chunk_len;
+    const uint64_t avail = remain < job.chunk_len ? remain : job.chunk_len;
+    const uint32_t my_blocks = static_cast<uint32_t>(avail >> 6);
+    const uint32_t rem = ends_now ? static_cast<uint32_t>(avail & 63u) : 0u;
+    const uint8_t* src = job.data + m * job.stride;
+
+    Lane<GH_SHA1, false> L;
+    L.one = 1;
+    if (job.prior == 0 || done_before) L.init();
+    else L.load(job.state, job.n_msgs, m);
+#pragma unroll 1
+    for (uint32_t q = 0; q < n_batches; q++) {
+        const uint32_t p = q & 1u;
+        mbar_wait(w_full + 8 * p, (q >> 1) & 1u);
+        const uint32_t wk0 = wk + p * kTrioH * kTrioWkBlock + lane * 16;
+#pragma unroll 1
+        for (uint32_t j = 0; j < kTrioH && q * kTrioH + j < n_blocks; j++)
+#if GH_TRIO_DEBUG != 1
+            if (q * kTrioH + j < my_blocks) sha1_rounds(L.s1, wk0 + j * kTrioWkBlock, job.one);
+#endif
+        __syncwarp();
+        if (lane == 0) mbar_arrive1(w_empty + 8 * p);
+    }
+    bool ok = false;
+    if (active && !done_before) {
+        if (ends_now) {
+            finalize<GH_SHA1, false>(L, src + static_cast<uint64_t>(my_blocks) * 64, rem, total_m);
+            ok = emit<GH_SHA1, false>(L, job, m);
+        } else {
+            L.store(job.state, job.n_msgs, m);
+        }
+    }
+    __syncwarp();
+    if (job.ok_words) {
+        const uint32_t okmask = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0 && okmask) {
+            const uint64_t bit0 = job.ok_base + m;
+            const uint32_t sh = static_cast<uint32_t>(bit0 & 31u);
+            atomicOr(job.ok_words + (bit0 >> 5), okmask << sh);
+            if (sh && (okmask >> (32 - sh))) atomicOr(job.ok_words + (bit0 >> 5) + 1, okmask >> (32 - sh));
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------- synthetic stream
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -738,15 +936,33 @@ int split_max_warps_per_sm() {
     static const int v = env_int("GPUHASH_SPLIT_WARPS_PER_SM", 2);
     return v;
 }
+// The trio kernel (per chain one rounds-warp fed by two schedule-warps, up to three chains per SM)
+// serves staged SHA-1 batches of at most this many message-warps per SM (0 disables it; the lane
+// and 1R+1S split kernels then take over as before).
+int trio_max_warps_per_sm() {
+    static const int v = env_int("GPUHASH_TRIO_WARPS_PER_SM", kTrioMaxChains);
+    return v;
+}
 int forced_tps() {
     static const int v = env_int("GPUHASH_TPS", 0);
     return v;
+}
+
+// Name of the hashing kernel this host thread launched last (gh_last_kernel): tests assert on the
+// path taken, bench.py looks the kernel's instruction mix up in the shipped SASS under this name.
+thread_local const char* g_last_kernel = "";
+template <int ALGOS, bool STAGED, bool FMA, int TPS>
+const char* lanes_name() {
+    static const std::string n = "gh_hash_lanes<" + std::to_string(ALGOS) + ", " + (STAGED ? "1" : "0") + ", " + (FMA ? "1" : "0") +
+                                 ", " + std::to_string(TPS) + ">";
+    return n.c_str();
 }
 
 template <int ALGOS, bool FMA, int TPS>
 cudaError_t launch_staged(const GhJob& job, const CUtensorMap& tmap, unsigned blocks, int wpb, cudaStream_t stream) {
     const size_t smem = static_cast<size_t>(wpb) * (warp_smem(TPS) + 8 * kStages);
     gh_hash_lanes<ALGOS, true, FMA, TPS><<<dim3(blocks), dim3(32 * wpb), smem, stream>>>(tmap, job);
+    g_last_kernel = lanes_name<ALGOS, true, FMA, TPS>();
     return cudaGetLastError();
 }
 
@@ -762,6 +978,23 @@ cudaError_t launch_split(const GhJob& job_in, uint64_t count, const CUtensorMap&
     if (nblocks > 0x7fffffffull) return cudaErrorInvalidValue;
     gh_hash_split<ALGO, WITH_MD5><<<dim3(static_cast<unsigned>(nblocks)), dim3(WITH_MD5 ? 96 : 64), split_smem<ALGO>(),
                                     stream>>>(tmap, job);
+    g_last_kernel = ALGO == GH_SHA1 ? "gh_hash_split<1, 0>" : WITH_MD5 ? "gh_hash_split<4, 1>" : "gh_hash_split<4, 0>";
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trio(const GhJob& job_in, uint64_t count, int chains, const CUtensorMap& tmap, uint32_t inner_words,
+                        cudaStream_t stream) {
+    GhJob job = job_in;
+    job.first_msg = 0;
+    job.count = count;
+    job.tma_inner = inner_words;
+    job.one = 1;
+    job.chains_per_cta = static_cast<uint32_t>(chains);
+    const uint64_t n_mw = (count + 31) / 32;
+    const uint64_t nblocks = (n_mw + chains - 1) / chains;
+    if (nblocks > 0x7fffffffull) return cudaErrorInvalidValue;
+    gh_hash_trio<<<dim3(static_cast<unsigned>(nblocks)), dim3(32 * trio_warps(chains)), trio_smem(chains), stream>>>(tmap, job);
+    g_last_kernel = "gh_hash_trio";
     return cudaGetLastError();
 }
 
@@ -789,6 +1022,7 @@ cudaError_t launch_range(const GhJob& job_in, uint64_t first, uint64_t count, bo
     }
     if (fma) gh_hash_lanes<ALGOS, false, true, 2><<<dim3(blocks), dim3(32 * wpb), 0, stream>>>(tmap, job);
     else gh_hash_lanes<ALGOS, false, false, 2><<<dim3(blocks), dim3(32 * wpb), 0, stream>>>(tmap, job);
+    if (count > 1) g_last_kernel = fma ? lanes_name<ALGOS, false, true, 2>() : lanes_name<ALGOS, false, false, 2>();  // not the 1-message tail launch
     return cudaGetLastError();
 }
 
@@ -819,6 +1053,22 @@ cudaError_t launch_algo(const GhJob& job, int sm_count, cudaStream_t stream) {
     int tps = warps > sms * 6 ? 2 : 4;
     if (forced_tps() == 2 || forced_tps() == 4) tps = forced_tps();
     cudaError_t e;
+    if constexpr (ALGOS == GH_SHA1) {
+        const uint64_t tw = static_cast<uint64_t>(trio_max_warps_per_sm());
+        // One chain per SM: rounds warp and both schedule warps each have a sub-partition to themselves.
+        // Three per SM (more than two message-warps per SM, where the 1R+1S split below no longer has a
+        // sub-partition for every warp): rounds and schedule warps share sub-partitions, still ahead of the
+        // lane kernel. In between (two per SM) the 1R+1S split is faster -- two CTAs of two warps give every
+        // warp its own sub-partition (measured: profiles/r02_ab_sha1_kernels.jsonl).
+        const int chains = static_cast<int>(std::min<uint64_t>(kTrioMaxChains, (warps + sms - 1) / sms));
+        if (staged && tw && warps <= sms * std::min<uint64_t>(tw, kTrioMaxChains) &&
+            (chains != 2 || split_max_warps_per_sm() < 2)) {
+            e = launch_trio(job, tma_rows, chains, tmap, static_cast<uint32_t>(inner_words), stream);
+            if (e != cudaSuccess) return e;
+            if (last_short) e = launch_range<ALGOS>(job, job.n_msgs - 1, 1, false, tmap, 0, 1, tps, stream);
+            return e;
+        }
+    }
     if (staged && ALGOS != GH_MD5 && warps <= sms * static_cast<uint64_t>(split_max_warps_per_sm())) {
         // too few chains to fill the machine: spend the idle sub-partitions on the message schedule
         if constexpr (ALGOS == GH_SHA1) e = launch_split<GH_SHA1, false>(job, tma_rows, tmap, static_cast<uint32_t>(inner_words), stream);
@@ -876,6 +1126,10 @@ cudaError_t gh_kernels_init_device() {
     if ((e = init_split<GH_SHA1, false>()) != cudaSuccess) return e;
     if ((e = init_split<GH_SHA256, false>()) != cudaSuccess) return e;
     if ((e = init_split<GH_SHA256, true>()) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(gh_hash_trio, cudaFuncAttributeMaxDynamicSharedMemorySize, trio_smem(kTrioMaxChains))) != cudaSuccess)
+        return e;
+    if ((e = cudaFuncSetAttribute(gh_hash_trio, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess)
+        return e;
     return encode_tiled() ? cudaSuccess : cudaErrorNotSupported;
 }
 
@@ -888,6 +1142,8 @@ cudaError_t gh_launch_hash(int algos, const GhJob& job, int sm_count, cudaStream
         default: return cudaErrorInvalidValue;
     }
 }
+
+extern "C" const char* gh_last_kernel(void) { return g_last_kernel; }
 
 cudaError_t gh_launch_generate(uint8_t* d_out, uint64_t seed, uint64_t offset, uint64_t len, cudaStream_t stream) {
     if (len == 0) return cudaSuccess;

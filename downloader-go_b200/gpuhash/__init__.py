@@ -21,7 +21,7 @@ import numpy as np
 SHA1, MD5, SHA256 = 1, 2, 4
 DIGEST_LEN = {SHA1: 20, MD5: 16, SHA256: 32}
 
-GH_OK, GH_EINVAL, GH_ENODEVICE, GH_ENOMEM, GH_ECUDA, GH_ECTX_LOST, GH_ERANGE = range(7)
+GH_OK, GH_EINVAL, GH_ENODEVICE, GH_ENOMEM, GH_ECUDA, GH_ECTX_LOST, GH_ERANGE, GH_EIO = range(8)
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("GPUHASH_LIB") or os.path.join(_PKG, "libgpuhash.so")
@@ -63,6 +63,8 @@ ABI = {
     "gh_device_count": (_INT, [_VP]),
     "gh_get_stats": (_INT, [_VP, ctypes.POINTER(Stats)]),
     "gh_version": (ctypes.c_char_p, []),
+    "gh_last_kernel": (ctypes.c_char_p, []),
+    "gh_debug_fail_nth_copy": (_INT, [_VP, ctypes.c_int64]),
     "gh_verify_pieces": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_hash_parts": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _INT, _VP, _VP, _VP]),
     "gh_s3_etag": (_INT, [_VP, _VP, _U64, ctypes.c_char_p, _SZ]),
@@ -140,6 +142,12 @@ def hash_update_device_noalloc(cuda_device, algos, d_data, stride, chunk_len, pr
                                               vp(stream) if stream else None)
     if rc:
         raise GpuHashError(rc, "gh_hash_update_device_noalloc")
+
+
+def last_kernel():
+    """Name of the hashing kernel variant this thread launched last (device-resident calls launch on
+    the calling thread; host-buffer calls on a context with one device do too)."""
+    return load().gh_last_kernel().decode()
 
 
 def shard_range(n_msgs, n_shards, shard):

@@ -42,7 +42,10 @@ enum {
     GH_ENOMEM = 3,     /* host or device allocation failed */
     GH_ECUDA = 4,      /* a CUDA call failed; gh_last_error(ctx) has the text */
     GH_ECTX_LOST = 5,  /* sticky device error: destroy the context */
-    GH_ERANGE = 6      /* size beyond a documented limit */
+    GH_ERANGE = 6,     /* size beyond a documented limit */
+    GH_EIO = 7         /* a payload file could not be opened or read (EACCES, EMFILE, EIO ...); gh_last_error names it.
+                          A file that does not exist (ENOENT) or is shorter than promised is NOT an error: its
+                          missing bytes read as zeros and the pieces over them fail verification */
 };
 
 enum { GH_SHA1 = 1, GH_MD5 = 2, GH_SHA256 = 4 }; /* algos bitmask; GH_MD5|GH_SHA256 = one fused pass */
@@ -77,10 +80,25 @@ typedef struct {
 int         gh_create(gh_ctx** out, const gh_config* cfg /* NULL = defaults */);
 void        gh_destroy(gh_ctx* ctx);
 const char* gh_strerror(int status);
-const char* gh_last_error(gh_ctx* ctx);           /* detail of the last failure on this context */
+const char* gh_last_error(gh_ctx* ctx);           /* detail of the last failure on this context; the pointer stays
+                                                     valid until the calling thread's next gh_last_error */
 int         gh_device_count(gh_ctx* ctx);
 int         gh_get_stats(gh_ctx* ctx, gh_stats* out);
 const char* gh_version(void);
+/* Name of the hashing kernel variant the calling thread launched last ("gh_hash_trio",
+ * "gh_hash_lanes<1, 1, 1, 4>", ...; "" before the first launch). Diagnostic: which of the kernels of
+ * DESIGN.md section 4 a batch shape was routed to. No reference counterpart. */
+const char* gh_last_kernel(void);
+
+/* Error contract of the calls below: a call that fails has first waited for every copy and kernel it
+ * had queued, so no DMA is still reading the caller's buffers when it returns, and it leaves the
+ * context usable for the next call -- unless the status is GH_ECTX_LOST (a device fault: destroy the
+ * context). Outputs of a failed call are unspecified. */
+
+/* Test hook (no reference counterpart): the n-th payload copy (host->device, counted from 0 over
+ * the following calls on this context) fails with GH_ECUDA as if the CUDA runtime had refused it;
+ * n < 0 disarms. Exists so that the error contract above can be exercised on a healthy GPU. */
+int gh_debug_fail_nth_copy(gh_ctx* ctx, int64_t n);
 
 /* ---- host-buffer (end-to-end) entry points -------------------------------------------------- */
 

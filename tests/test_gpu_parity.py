@@ -356,13 +356,14 @@ def test_stats_report_launches_and_bytes(gh):
 
 
 def test_lane_kernels_with_role_split_disabled():
-    """Small batches normally take the role-split kernels (schedule / rounds / MD5 warps); the
-    library reads its tuning switches once per process, so the one-message-per-lane kernels are
-    exercised on the same cases in a child process with the split switched off."""
+    """Small batches normally take the role-split kernels (trio for SHA-1; schedule / rounds / MD5
+    warps for the others); the library reads its tuning switches once per process, so the
+    one-message-per-lane kernels are exercised on the same cases in a child process with both
+    switched off."""
     import os
     import subprocess
     import sys
-    env = dict(os.environ, GPUHASH_SPLIT_WARPS_PER_SM="0")
+    env = dict(os.environ, GPUHASH_SPLIT_WARPS_PER_SM="0", GPUHASH_TRIO_WARPS_PER_SM="0")
     here = os.path.abspath(__file__)
     r = subprocess.run([sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-k",
                         "differential or chunk_interleaved or resumable or cfg5 or padding or cfg3"],
