@@ -847,6 +847,8 @@ int run_device_body(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint6
 
 int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8_t* expected, uint8_t* sha1_out,
               uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad, bool per_run = false);
+int run_table(gh_ctx* c, SpanIndex& ix, const MsgTable& T, int algos, const uint8_t* expected, uint8_t* sha1_out,
+              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad);
 
 int run_batch(gh_ctx* c, const gh_span* spans, size_t n_spans, uint64_t msg_len, int algos, const uint8_t* expected,
               uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad,
@@ -883,7 +885,6 @@ int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8
     if (msg_len == 0) return fail(c, GH_EINVAL, "message length must be > 0");
     if (!(algos & (GH_SHA1 | GH_MD5 | GH_SHA256)) || (algos & ~(GH_SHA1 | GH_MD5 | GH_SHA256)))
         return fail(c, GH_EINVAL, "algos must be a mask of GH_SHA1|GH_MD5|GH_SHA256");
-    const auto t0 = std::chrono::steady_clock::now();
     MsgTable T;
     T.L = msg_len;
     T.total = ix.total();
@@ -899,6 +900,15 @@ int run_index(gh_ctx* c, SpanIndex& ix, uint64_t msg_len, int algos, const uint8
     } else {
         T.n = count_msgs(T.total, msg_len);
     }
+    return run_table(c, ix, T, algos, expected, sha1_out, md5_out, sha256_out, bitmap, n_bad);
+}
+
+// caller holds c->mu and has checked lost / stream_open / algos. The batch proper: shard the table's
+// messages over the context's devices, run, merge.
+int run_table(gh_ctx* c, SpanIndex& ix, const MsgTable& T, int algos, const uint8_t* expected, uint8_t* sha1_out,
+              uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad) {
+    const auto t0 = std::chrono::steady_clock::now();
+    const uint64_t msg_len = T.L;
     const uint64_t n = T.n;
     if (n_bad) *n_bad = 0;
     if (n == 0) {
@@ -1334,6 +1344,267 @@ void gh_stream_abort(gh_stream* st) {
         for (auto& sl : d.slots) sl.h2d_pending = false;
     }
     stream_release(st);
+}
+
+// ---- micro-batcher for live pieces ------------------------------------------------------------
+// anacrolix/torrent hashes a piece the moment its last chunk arrives, about two at a time, from
+// its own goroutines (reference torrent.go:79 t.DownloadAll() ... :106 client.WaitAll()). A GPU wants
+// hundreds of pieces per launch. The batcher is the adapter between the two: any number of threads
+// hand it ONE piece each and block; it collects them in a pinned buffer and runs the whole lot as one
+// batch when `max_pieces` are waiting or the oldest has waited `max_delay_ms`; every caller wakes with
+// the verdict of ITS piece. Pieces arrive in any order and with any index; only their bytes, length
+// and expected digest matter. A failure of the batch (CUDA error, lost context) reaches every caller
+// of that batch as a STATUS, never as "hash mismatch": the caller falls back to hashing on the CPU,
+// it must not re-download good data.
+struct gh_batcher {
+    gh_ctx* c = nullptr;
+    uint64_t piece_len = 0;
+    uint32_t max_pieces = 0;
+    uint32_t max_delay_ms = 0;
+
+    struct Batch {
+        uint8_t* buf = nullptr;            // pinned, max_pieces * piece_len
+        std::vector<uint64_t> len;         // per slot
+        std::vector<uint8_t> expected;     // 20 per slot
+        std::vector<uint8_t> digest;       // 20 per slot (result)
+        std::vector<uint64_t> bitmap;      // result
+        uint32_t reserved = 0;             // slots handed out
+        uint32_t committed = 0;            // slots whose bytes and expected digest are in place (or that were cancelled)
+        uint32_t readers = 0;              // callers that still have to pick up their verdict
+        uint64_t seq = 0;                  // which use of this buffer (verdicts are picked up by (buffer, seq))
+        bool closed = false;               // no more reservations: queued for or in flight on the GPU
+        bool done = false;                 // results are in
+        int status = GH_OK;                // of the whole batch
+        std::chrono::steady_clock::time_point first;
+    };
+    Batch b[2];
+    int filling = 0;
+    std::mutex mu;
+    std::condition_variable cv_callers;  // space available / verdict ready
+    std::condition_variable cv_flusher;  // a batch became runnable, or its deadline needs re-arming
+    std::thread flusher;
+    bool stop = false;
+    uint32_t active_calls = 0;
+    gh_batcher_stats st{};
+};
+
+namespace {
+
+// One batch through the ring: messages k = 0..n-1 at buf + k*piece_len with their own lengths.
+int batcher_run(gh_batcher* B, gh_batcher::Batch& bt) {
+    gh_ctx* c = B->c;
+    const uint32_t n = bt.reserved;
+    std::lock_guard<std::mutex> g(c->mu);
+    if (c->lost) return fail(c, GH_ECTX_LOST, "context lost after a device fault");
+    if (c->stream_open) return fail(c, GH_EINVAL, "a gh_stream is open on this context; finish or abort it first");
+    SpanIndex ix;
+    gh_span sp{bt.buf, static_cast<uint64_t>(n) * B->piece_len};
+    build_index(&sp, 1, &ix);
+    MsgTable T;
+    T.L = B->piece_len;
+    T.total = sp.len;
+    T.n = n;
+    for (uint32_t k = 0; k < n; k++) {
+        T.off_.push_back(static_cast<uint64_t>(k) * B->piece_len);
+        T.len_.push_back(bt.len[k]);
+    }
+    std::fill(bt.bitmap.begin(), bt.bitmap.end(), 0);
+    return run_table(c, ix, T, GH_SHA1, bt.expected.data(), bt.digest.data(), nullptr, nullptr, bt.bitmap.data(), nullptr);
+}
+
+void batcher_loop(gh_batcher* B) {
+    std::unique_lock<std::mutex> lk(B->mu);
+    for (;;) {
+        gh_batcher::Batch& bt = B->b[B->filling];
+        // runnable: something is waiting, every reserved slot has been filled, and the batch is full,
+        // overdue, or was closed by gh_batcher_flush / destroy
+        auto runnable = [&] {
+            if (bt.done || bt.reserved == 0 || bt.committed < bt.reserved) return false;  // done: waiting for its readers
+            if (bt.closed || bt.reserved >= B->max_pieces || B->stop) return true;
+            return std::chrono::steady_clock::now() >= bt.first + std::chrono::milliseconds(B->max_delay_ms);
+        };
+        while (!runnable()) {
+            if (B->stop && bt.reserved == 0) return;
+            if (!bt.done && bt.reserved > 0 && bt.committed == bt.reserved && !bt.closed)
+                B->cv_flusher.wait_until(lk, bt.first + std::chrono::milliseconds(B->max_delay_ms));
+            else
+                B->cv_flusher.wait(lk);
+        }
+        const bool by_deadline = !bt.closed && bt.reserved < B->max_pieces;
+        bt.closed = true;
+        // new pieces go to the other buffer while this one is on the GPU (once its verdicts are picked up)
+        B->filling ^= 1;
+        B->cv_callers.notify_all();
+        lk.unlock();
+        const int rc = batcher_run(B, bt);
+        lk.lock();
+        bt.status = rc;
+        bt.done = true;
+        B->st.batches++;
+        B->st.pieces += bt.reserved;
+        if (by_deadline) B->st.flushed_by_deadline++;
+        else B->st.flushed_full++;
+        if (rc != GH_OK) B->st.failed_batches++;
+        if (bt.readers == 0) {  // only cancelled slots: nobody will pick anything up
+            bt.reserved = bt.committed = 0;
+            bt.closed = bt.done = false;
+            bt.seq++;
+        }
+        B->cv_callers.notify_all();
+    }
+}
+
+}  // namespace
+
+int gh_batcher_create(gh_ctx* ctx, uint64_t piece_len, uint32_t max_pieces, uint32_t max_delay_ms, gh_batcher** out) {
+    if (!ctx || !out) return GH_EINVAL;
+    *out = nullptr;
+    if (piece_len == 0 || max_pieces == 0) return fail(ctx, GH_EINVAL, "gh_batcher_create: piece_len and max_pieces must be > 0");
+    const uint64_t bytes = piece_len * max_pieces;
+    if (bytes / max_pieces != piece_len || bytes > (4ull << 30))
+        return fail(ctx, GH_ERANGE, "gh_batcher_create: max_pieces * piece_len is limited to 4 GiB per batch buffer");
+    gh_batcher* B = new gh_batcher();
+    B->c = ctx;
+    B->piece_len = piece_len;
+    B->max_pieces = max_pieces;
+    B->max_delay_ms = max_delay_ms;
+    for (auto& bt : B->b) {
+        if (cudaHostAlloc(reinterpret_cast<void**>(&bt.buf), bytes, cudaHostAllocPortable) != cudaSuccess) {
+            cudaGetLastError();
+            for (auto& x : B->b)
+                if (x.buf) cudaFreeHost(x.buf);
+            delete B;
+            return fail(ctx, GH_ENOMEM, "gh_batcher_create: pinned batch buffers");
+        }
+        bt.len.assign(max_pieces, 0);
+        bt.expected.assign(20ull * max_pieces, 0);
+        bt.digest.assign(20ull * max_pieces, 0);
+        bt.bitmap.assign((max_pieces + 63) / 64 + 1, 0);
+    }
+    B->flusher = std::thread(batcher_loop, B);
+    *out = B;
+    return GH_OK;
+}
+
+int gh_batcher_reserve(gh_batcher* B, uint64_t len, gh_batch_slot* slot, void** buf) {
+    if (!B || !slot || !buf) return GH_EINVAL;
+    if (len > B->piece_len) return GH_ERANGE;
+    std::unique_lock<std::mutex> lk(B->mu);
+    if (B->stop) return GH_EINVAL;
+    B->active_calls++;
+    for (;;) {
+        gh_batcher::Batch& bt = B->b[B->filling];
+        if (!bt.closed && bt.reserved < B->max_pieces) {
+            const uint32_t k = bt.reserved++;
+            if (k == 0) {
+                bt.first = std::chrono::steady_clock::now();
+                bt.status = GH_OK;
+            }
+            bt.len[k] = len;
+            slot->buffer = B->filling;
+            slot->index = k;
+            slot->seq = bt.seq;
+            *buf = bt.buf + static_cast<uint64_t>(k) * B->piece_len;
+            B->active_calls--;
+            return GH_OK;
+        }
+        if (B->stop) {
+            B->active_calls--;
+            B->cv_callers.notify_all();
+            return GH_EINVAL;
+        }
+        B->cv_callers.wait(lk);  // both buffers busy: the GPU batch or its readers are still at work
+    }
+}
+
+static int batcher_finish_slot(gh_batcher* B, const gh_batch_slot* slot, const uint8_t* expected20, bool cancel, int* ok_out,
+                               uint8_t* digest_out) {
+    if (!B || !slot || slot->buffer > 1) return GH_EINVAL;
+    std::unique_lock<std::mutex> lk(B->mu);
+    gh_batcher::Batch& bt = B->b[slot->buffer];
+    if (slot->seq != bt.seq || slot->index >= bt.reserved || bt.done) return GH_EINVAL;
+    if (cancel) {
+        bt.len[slot->index] = 0;  // hashed as an empty message, verdict ignored
+        memset(&bt.expected[20ull * slot->index], 0, 20);
+    } else {
+        if (!expected20) return GH_EINVAL;
+        memcpy(&bt.expected[20ull * slot->index], expected20, 20);
+        bt.readers++;
+    }
+    bt.committed++;
+    B->cv_flusher.notify_one();
+    if (cancel) return GH_OK;
+    B->active_calls++;
+    const uint64_t seq = bt.seq;
+    B->cv_callers.wait(lk, [&] { return bt.done && bt.seq == seq; });
+    const int rc = bt.status;
+    if (rc == GH_OK) {
+        if (ok_out) *ok_out = static_cast<int>((bt.bitmap[slot->index >> 6] >> (slot->index & 63)) & 1);
+        if (digest_out) memcpy(digest_out, &bt.digest[20ull * slot->index], 20);
+    }
+    if (--bt.readers == 0) {  // last verdict picked up: the buffer can fill again
+        bt.reserved = bt.committed = 0;
+        bt.closed = bt.done = false;
+        bt.seq++;
+    }
+    B->active_calls--;
+    B->cv_callers.notify_all();
+    return rc;
+}
+
+int gh_batcher_commit(gh_batcher* B, const gh_batch_slot* slot, const uint8_t* expected20, int* ok_out, uint8_t* digest_out) {
+    return batcher_finish_slot(B, slot, expected20, false, ok_out, digest_out);
+}
+
+int gh_batcher_cancel(gh_batcher* B, const gh_batch_slot* slot) {
+    return batcher_finish_slot(B, slot, nullptr, true, nullptr, nullptr);
+}
+
+int gh_batcher_verify(gh_batcher* B, const void* data, uint64_t len, const uint8_t* expected20, int* ok_out,
+                      uint8_t* digest_out) {
+    if (!B || (len && !data) || !expected20) return GH_EINVAL;
+    gh_batch_slot slot;
+    void* buf = nullptr;
+    int rc = gh_batcher_reserve(B, len, &slot, &buf);
+    if (rc) return rc;
+    memcpy(buf, data, len);  // on the caller's thread: many callers copy in parallel
+    return gh_batcher_commit(B, &slot, expected20, ok_out, digest_out);
+}
+
+int gh_batcher_flush(gh_batcher* B) {
+    if (!B) return GH_EINVAL;
+    std::lock_guard<std::mutex> g(B->mu);
+    gh_batcher::Batch& bt = B->b[B->filling];
+    if (bt.reserved > 0) bt.closed = true;  // runs as soon as every reserved slot is committed
+    B->cv_flusher.notify_one();
+    return GH_OK;
+}
+
+int gh_batcher_get_stats(gh_batcher* B, gh_batcher_stats* out) {
+    if (!B || !out) return GH_EINVAL;
+    std::lock_guard<std::mutex> g(B->mu);
+    *out = B->st;
+    return GH_OK;
+}
+
+void gh_batcher_destroy(gh_batcher* B) {
+    if (!B) return;
+    {
+        std::unique_lock<std::mutex> lk(B->mu);
+        B->stop = true;  // no new reservations; what is waiting is flushed so that no caller hangs
+        B->cv_flusher.notify_all();
+        B->cv_callers.notify_all();
+        B->cv_callers.wait(lk, [&] {
+            for (auto& bt : B->b)
+                if (bt.readers || bt.reserved != bt.committed || (bt.reserved && !bt.done)) return false;
+            return B->active_calls == 0;
+        });
+    }
+    B->cv_flusher.notify_all();
+    if (B->flusher.joinable()) B->flusher.join();
+    for (auto& bt : B->b)
+        if (bt.buf) cudaFreeHost(bt.buf);
+    delete B;
 }
 
 // ---- device-resident -----------------------------------------------------------------------

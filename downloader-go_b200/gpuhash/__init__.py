@@ -46,6 +46,15 @@ class File(ctypes.Structure):
     _fields_ = [("path", ctypes.c_char_p), ("len", ctypes.c_uint64)]
 
 
+class BatchSlot(ctypes.Structure):
+    _fields_ = [("buffer", ctypes.c_uint32), ("index", ctypes.c_uint32), ("seq", ctypes.c_uint64)]
+
+
+class BatcherStats(ctypes.Structure):
+    _fields_ = [("batches", ctypes.c_uint64), ("pieces", ctypes.c_uint64), ("flushed_full", ctypes.c_uint64),
+                ("flushed_by_deadline", ctypes.c_uint64), ("failed_batches", ctypes.c_uint64)]
+
+
 class Stats(ctypes.Structure):
     _fields_ = [("kernel_launches", ctypes.c_uint64), ("h2d_bytes", ctypes.c_uint64),
                 ("d2h_bytes", ctypes.c_uint64), ("kernel_ms", ctypes.c_double), ("wall_ms", ctypes.c_double)]
@@ -75,6 +84,14 @@ ABI = {
     "gh_stream_submit": (_INT, [_VP, _U64]),
     "gh_stream_finish": (_INT, [_VP, _VP, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_stream_abort": (None, [_VP]),
+    "gh_batcher_create": (_INT, [_VP, _U64, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(_VP)]),
+    "gh_batcher_verify": (_INT, [_VP, _VP, _U64, _VP, ctypes.POINTER(_INT), _VP]),
+    "gh_batcher_reserve": (_INT, [_VP, _U64, ctypes.POINTER(BatchSlot), ctypes.POINTER(_VP)]),
+    "gh_batcher_commit": (_INT, [_VP, ctypes.POINTER(BatchSlot), _VP, ctypes.POINTER(_INT), _VP]),
+    "gh_batcher_cancel": (_INT, [_VP, ctypes.POINTER(BatchSlot)]),
+    "gh_batcher_flush": (_INT, [_VP]),
+    "gh_batcher_get_stats": (_INT, [_VP, ctypes.POINTER(BatcherStats)]),
+    "gh_batcher_destroy": (None, [_VP]),
     "gh_hash_parts_per_file": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _INT, _VP, _VP, _VP]),
     "gh_hash_file_parts_per_file": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _INT, _VP, _VP, _VP]),
     "gh_metainfo_parse": (_INT, [_VP, _SZ, ctypes.POINTER(_VP), ctypes.c_char_p, _SZ]),
@@ -286,6 +303,62 @@ class Stream:
             self.h = None
 
 
+class Batcher:
+    """gh_batcher_*: the micro-batcher a replaced Torrent.hashPiece would call (Go: gpustorage.Batcher).
+    verify() blocks until the piece's verdict is known; call it from as many threads as pieces should
+    share a batch (ctypes releases the GIL for the duration). A failed batch raises GpuHashError --
+    the caller's cue to hash on the CPU -- and is never reported as a mismatch."""
+
+    def __init__(self, ctx, piece_len, max_pieces, max_delay_ms):
+        self.ctx = ctx
+        h = ctypes.c_void_p()
+        ctx._check(ctx.L.gh_batcher_create(ctx.h, piece_len, max_pieces, max_delay_ms, ctypes.byref(h)), "gh_batcher_create")
+        self.h = h
+
+    def verify(self, data, expected20, want_digest=False):
+        a = _u8(data)
+        e = _u8(expected20)
+        ok = ctypes.c_int(-1)
+        dig = np.zeros(20, dtype=np.uint8) if want_digest else None
+        rc = self.ctx.L.gh_batcher_verify(self.h, _ptr(a), a.size, _ptr(e), ctypes.byref(ok), _ptr(dig))
+        if rc:
+            raise GpuHashError(rc, "gh_batcher_verify", self.ctx.L.gh_last_error(self.ctx.h).decode())
+        return (bool(ok.value), dig.tobytes()) if want_digest else bool(ok.value)
+
+    def reserve(self, length):
+        """-> (slot, numpy view of the pinned slot of `length` bytes) for in-place producers."""
+        slot, buf = BatchSlot(), ctypes.c_void_p()
+        rc = self.ctx.L.gh_batcher_reserve(self.h, length, ctypes.byref(slot), ctypes.byref(buf))
+        if rc:
+            raise GpuHashError(rc, "gh_batcher_reserve")
+        view = np.ctypeslib.as_array((ctypes.c_uint8 * max(length, 1)).from_address(buf.value))[:length]
+        return slot, view
+
+    def commit(self, slot, expected20):
+        e = _u8(expected20)
+        ok = ctypes.c_int(-1)
+        rc = self.ctx.L.gh_batcher_commit(self.h, ctypes.byref(slot), _ptr(e), ctypes.byref(ok), None)
+        if rc:
+            raise GpuHashError(rc, "gh_batcher_commit", self.ctx.L.gh_last_error(self.ctx.h).decode())
+        return bool(ok.value)
+
+    def cancel(self, slot):
+        return self.ctx.L.gh_batcher_cancel(self.h, ctypes.byref(slot))
+
+    def flush(self):
+        self.ctx.L.gh_batcher_flush(self.h)
+
+    def stats(self):
+        s = BatcherStats()
+        self.ctx.L.gh_batcher_get_stats(self.h, ctypes.byref(s))
+        return s
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.L.gh_batcher_destroy(self.h)
+            self.h = None
+
+
 class Context:
     """One gh_ctx. `devices` is a list of CUDA ordinals (None = all visible)."""
 
@@ -429,6 +502,9 @@ class Context:
 
     def Stream(self, algos, msg_len, total_len, expected=None):
         return Stream(self, algos, msg_len, total_len, expected)
+
+    def Batcher(self, piece_len, max_pieces, max_delay_ms):
+        return Batcher(self, piece_len, max_pieces, max_delay_ms)
 
     def S3ETag(self, part_md5s):
         a = _u8(part_md5s)

@@ -163,6 +163,50 @@ int  gh_stream_finish(gh_stream* st, uint8_t* sha1_out, uint8_t* md5_out, uint8_
                       uint64_t* ok_bitmap_out, uint64_t* n_bad_out);
 void gh_stream_abort(gh_stream* st);
 
+/* ---- micro-batcher for live pieces ----------------------------------------------------------------- */
+/* The seam for a LIVE download: anacrolix/torrent calls Torrent.hashPiece for one piece at a time, from
+ * up to PieceHashersPerTorrent goroutines, as pieces complete between torrent.go:79 (t.DownloadAll)
+ * and :106 (client.WaitAll). gh_batcher_verify is what a replaced hashPiece calls instead of
+ * crypto/sha1: it blocks until THIS piece's verdict is known, while the batcher turns the concurrent
+ * calls into GPU batches -- a batch runs when max_pieces are waiting or the oldest has waited
+ * max_delay_ms. Pieces may come in any order; the torrent's short last piece is just a smaller `len`.
+ * Any number of threads may call concurrently (raise PieceHashersPerTorrent to max_pieces or more: a
+ * batch is only as large as the number of callers that are blocked in it).
+ *
+ * Status: GH_OK = the verdict is valid (*ok_out 1 = digest matched expected20, 0 = mismatch;
+ * digest_out, optional, receives the 20-byte SHA-1). ANY OTHER status means the verdict is unknown --
+ * the GPU batch failed, every caller of that batch gets the same status -- and the caller must fall
+ * back to hashing the piece on the CPU. It is never reported as a mismatch, which would make the
+ * torrent client re-download good data and penalise the peer that sent it.
+ *
+ * gh_batcher_reserve / gh_batcher_commit are the same in two steps for callers that can produce the
+ * piece in place: reserve returns a slot of the pinned batch buffer, the caller reads the piece
+ * straight into it (io.ReadFull from the piece's storage reader), commit blocks for the verdict.
+ * A reservation that cannot be filled must be given back with gh_batcher_cancel: a batch does not run
+ * before every reserved slot is committed or cancelled.
+ *
+ * Batches run on all devices of the context (sharded like gh_verify_pieces) and are serialised with
+ * the context's other calls. gh_batcher_destroy flushes what is waiting and returns when every
+ * blocked caller has its answer; calls made after it has started are refused with GH_EINVAL. */
+typedef struct gh_batcher gh_batcher;
+typedef struct {
+    uint32_t buffer, index; /* opaque: which slot of which batch buffer */
+    uint64_t seq;
+} gh_batch_slot;
+typedef struct {
+    uint64_t batches, pieces, flushed_full, flushed_by_deadline, failed_batches;
+} gh_batcher_stats;
+int  gh_batcher_create(gh_ctx* ctx, uint64_t piece_len, uint32_t max_pieces, uint32_t max_delay_ms, gh_batcher** out);
+int  gh_batcher_verify(gh_batcher* b, const void* data, uint64_t len, const uint8_t* expected20, int* ok_out,
+                       uint8_t* digest_out);
+int  gh_batcher_reserve(gh_batcher* b, uint64_t len, gh_batch_slot* slot, void** buf);
+int  gh_batcher_commit(gh_batcher* b, const gh_batch_slot* slot, const uint8_t* expected20, int* ok_out,
+                       uint8_t* digest_out);
+int  gh_batcher_cancel(gh_batcher* b, const gh_batch_slot* slot);
+int  gh_batcher_flush(gh_batcher* b);   /* run what is waiting now, without waiting for count or deadline */
+int  gh_batcher_get_stats(gh_batcher* b, gh_batcher_stats* out);
+void gh_batcher_destroy(gh_batcher* b);
+
 /* ---- metainfo (BEP 3 .torrent / info dictionary) ------------------------------------------------- */
 /* The data format on the input side of piece verification. In the reference the info dictionary
  * arrives after client.AddMagnet (torrent.go:58) and is awaited at torrent.go:69 (<-t.GotInfo());
