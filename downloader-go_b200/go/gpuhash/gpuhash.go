@@ -22,6 +22,7 @@ import (
 	"errors"
 	"fmt"
 	"runtime"
+	"time"
 	"unsafe"
 )
 
@@ -483,4 +484,81 @@ func (s *Stream) Finish() (bitmap []uint64, sha1 []byte, bad uint64, err error) 
 	var nbad C.uint64_t
 	rc := C.gh_stream_finish(s.st, d, nil, nil, bm, &nbad)
 	return bitmap, sha1, uint64(nbad), status(s.h.ctx, rc, "gh_stream_finish")
+}
+
+// Abort drops a stream that cannot be completed (an error from Acquire / Submit, or a reader that
+// failed): the context is usable again afterwards.
+func (s *Stream) Abort() {
+	if s.st != nil {
+		C.gh_stream_abort(s.st)
+		s.st = nil
+	}
+}
+
+// NewFromEnv creates a hasher configured the way the reference configures everything else -- from
+// the environment (GPUHASH_DEVICES, GPUHASH_SLOT_MIB, GPUHASH_SLOTS, GPUHASH_STAGE_THREADS; see
+// gh_config_from_env). It returns ErrDisabled when GPUHASH_DISABLE is set: the adapters then leave the
+// stock CPU paths of anacrolix / minio-go in place.
+func NewFromEnv() (*Hasher, error) {
+	var cfg C.gh_config
+	var devs [64]C.int
+	var disabled C.int
+	if rc := C.gh_config_from_env(&cfg, &devs[0], 64, &disabled); rc != C.GH_OK {
+		return nil, status(nil, rc, "gh_config_from_env")
+	}
+	if disabled != 0 {
+		return nil, ErrDisabled
+	}
+	h := &Hasher{}
+	rc := C.gh_create(&h.ctx, &cfg)
+	runtime.KeepAlive(&devs)
+	if err := status(nil, rc, "gh_create"); err != nil {
+		return nil, err
+	}
+	runtime.SetFinalizer(h, (*Hasher).Close)
+	return h, nil
+}
+
+// ErrDisabled: GPUHASH_DISABLE is set in the environment.
+var ErrDisabled = fmt.Errorf("gpuhash: disabled by GPUHASH_DISABLE")
+
+// Batcher is gh_batcher_*: many goroutines hand over one piece each and block for its verdict.
+type Batcher struct {
+	h *Hasher
+	b *C.gh_batcher
+}
+
+// Slot is a reserved place in the pinned batch buffer.
+type Slot struct{ s C.gh_batch_slot }
+
+func (h *Hasher) NewBatcher(pieceLen int64, maxPieces int, maxDelay time.Duration) (*Batcher, error) {
+	b := &Batcher{h: h}
+	rc := C.gh_batcher_create(h.ctx, C.uint64_t(pieceLen), C.uint32_t(maxPieces), C.uint32_t(maxDelay/time.Millisecond), &b.b)
+	return b, status(h.ctx, rc, "gh_batcher_create")
+}
+
+// Reserve returns a slot and its bytes (C memory, pinned): read the piece into them, then Commit or Cancel.
+func (b *Batcher) Reserve(length int64) (*Slot, []byte, error) {
+	var s Slot
+	var buf unsafe.Pointer
+	if rc := C.gh_batcher_reserve(b.b, C.uint64_t(length), &s.s, &buf); rc != C.GH_OK {
+		return nil, nil, status(b.h.ctx, rc, "gh_batcher_reserve")
+	}
+	return &s, unsafe.Slice((*byte)(buf), int(length)), nil
+}
+
+// Commit blocks until the batch has run. A non-nil error means "verdict unknown": hash on the CPU.
+func (b *Batcher) Commit(s *Slot, expected [20]byte) (bool, error) {
+	var ok C.int
+	rc := C.gh_batcher_commit(b.b, &s.s, (*C.uint8_t)(unsafe.Pointer(&expected[0])), &ok, nil)
+	return ok == 1, status(b.h.ctx, rc, "gh_batcher_commit")
+}
+
+func (b *Batcher) Cancel(s *Slot) { C.gh_batcher_cancel(b.b, &s.s) }
+
+func (b *Batcher) Close() {
+	if b.b != nil {
+		C.gh_batcher_destroy(b.b)
+		b.b = nil
+	}
 }

@@ -65,6 +65,7 @@ _lib = None
 # name -> (restype, argtypes); every symbol include/gpuhash.h declares
 _VP, _U64, _INT, _SZ = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_size_t
 ABI = {
+    "gh_config_from_env": (_INT, [ctypes.POINTER(Config), ctypes.POINTER(ctypes.c_int), _INT, ctypes.POINTER(_INT)]),
     "gh_create": (_INT, [ctypes.POINTER(_VP), ctypes.POINTER(Config)]),
     "gh_destroy": (None, [_VP]),
     "gh_strerror": (ctypes.c_char_p, [_INT]),
@@ -159,6 +160,20 @@ def hash_update_device_noalloc(cuda_device, algos, d_data, stride, chunk_len, pr
                                               vp(stream) if stream else None)
     if rc:
         raise GpuHashError(rc, "gh_hash_update_device_noalloc")
+
+
+class Disabled(RuntimeError):
+    """GPUHASH_DISABLE is set: the caller keeps its CPU path (the library has none of its own)."""
+
+
+def config_from_env():
+    """gh_config_from_env -> (devices or None, slot_bytes, slots, stage_threads, disabled)."""
+    cfg, devs, dis = Config(), (ctypes.c_int * 64)(), ctypes.c_int()
+    rc = load().gh_config_from_env(ctypes.byref(cfg), devs, 64, ctypes.byref(dis))
+    if rc:
+        raise GpuHashError(rc, "gh_config_from_env")
+    return ([devs[i] for i in range(cfg.n_devices)] if cfg.n_devices else None, int(cfg.slot_bytes), int(cfg.slots),
+            int(cfg.stage_threads), bool(dis.value))
 
 
 def last_kernel():
@@ -377,6 +392,15 @@ class Context:
             raise GpuHashError(rc, "gh_create")
         self.h = h
         self.L = L
+
+    @classmethod
+    def from_env(cls):
+        """The context the environment describes (GPUHASH_DEVICES / _SLOT_MIB / _SLOTS / _STAGE_THREADS);
+        raises Disabled when GPUHASH_DISABLE is set -- what the Go adapters do before installing themselves."""
+        devices, slot_bytes, slots, stage_threads, disabled = config_from_env()
+        if disabled:
+            raise Disabled("GPUHASH_DISABLE is set")
+        return cls(devices=devices, slot_bytes=slot_bytes, slots=slots, stage_threads=stage_threads)
 
     def close(self):
         if getattr(self, "h", None):

@@ -76,6 +76,20 @@ typedef struct {
     double   wall_ms;          /* host wall time of the LAST call */
 } gh_stats;
 
+/* Configuration from the environment, following the reference's convention (it reads RABBITMQ_ENDPOINT,
+ * S3_ENDPOINT, S3_ACCESS_KEY ... from the environment: cmd/downloader/downloader.go:54-58,
+ * internal/uploader/uploader.go:25, minio_credential_provider.go:24-25):
+ *   GPUHASH_DEVICES        comma-separated CUDA ordinals ("0,2,4,6")   -> cfg->devices (stored in devices_buf)
+ *   GPUHASH_SLOT_MIB       MiB per ring slot                           -> cfg->slot_bytes
+ *   GPUHASH_SLOTS          ring slots per device (>= 2)                -> cfg->slots
+ *   GPUHASH_STAGE_THREADS  host threads staging pageable spans / files -> cfg->stage_threads
+ *   GPUHASH_DISABLE        non-empty and not 0/false/no                -> *disabled = 1
+ * Unset or empty variables leave the field 0 (= library default). A malformed value is GH_EINVAL (more
+ * devices than devices_cap: GH_ERANGE) and nothing half-parsed is used. The library itself never
+ * computes on the CPU: `disabled` is for the adapters, which then do not install themselves and leave
+ * the stock crypto/sha1 / crypto/md5 paths in place. Host-only; needs no device. */
+int gh_config_from_env(gh_config* cfg, int* devices_buf, int devices_cap, int* disabled);
+
 /* ---- lifecycle ---------------------------------------------------------------------------- */
 int         gh_create(gh_ctx** out, const gh_config* cfg /* NULL = defaults */);
 void        gh_destroy(gh_ctx* ctx);
