@@ -181,7 +181,13 @@ def parallel_gen(oracle, seed, offset, ptr, n, threads):
 
 
 def openssl_rate(data, piece_len, threads):
-    """GB/s of OpenSSL's SHA-1 (SHA-NI where the CPU has it) through hashlib on `threads` threads."""
+    """GB/s of OpenSSL's SHA-1 (SHA-NI where the CPU has it) on `threads` threads: the C harness of
+    oracle/gh_openssl.c when it could be built, else hashlib (same library, Python call overhead)."""
+    import oracle
+    if oracle.openssl_lib() is not None:
+        t0 = time.perf_counter()
+        oracle.openssl_hash_msgs(oracle.SHA1, data, piece_len, threads)
+        return len(data) / (time.perf_counter() - t0) / 1e9
     import hashlib
     from concurrent.futures import ThreadPoolExecutor
     mv = memoryview(data)
@@ -239,7 +245,7 @@ def run_reference(args, out_fd):
     try:
         osl = data[: min(sample, 8 << 30)]
         cpu["openssl_sha_ni_gbs"] = round(openssl_rate(osl, PIECE_LEN, threads), 3)
-        cpu["openssl_sample"] = "first %.2f GiB, hashlib.sha1 on %d threads" % (osl.size / 2**30, threads)
+        cpu["openssl_sample"] = "first %.2f GiB, EVP_sha1 on %d threads" % (osl.size / 2**30, threads)
     except Exception:
         pass
     config = shared_config(total, world)

@@ -779,7 +779,11 @@ int run_device_body(gh_ctx* c, Device& d, const BatchArgs& A, uint64_t m0, uint6
         // so that all chains advance together; midstates stay in HBM. Rows that
         // lie inside one pinned span travel as a single strided (2-D) DMA.
         if ((rc = grow(c, &d.d_state, &d.d_state_cap, n * GH_STATE_WORDS * 4))) return rc;
-        const uint64_t gsz = std::min<uint64_t>(n, std::max<uint64_t>(1, S / kMinChunk));
+        // groups of equal size (a ragged last group of a few hundred chains would run chain-starved):
+        // as many groups as the per-message minimum chunk requires, messages spread evenly, whole warps
+        const uint64_t gmax = std::max<uint64_t>(1, S / kMinChunk);
+        const uint64_t n_groups = (n + gmax - 1) / gmax;
+        const uint64_t gsz = std::min<uint64_t>(gmax, (((n + n_groups - 1) / n_groups) + 31) & ~31ull);
         uint64_t b = 0;
         for (uint64_t g0 = m0; g0 < m1; g0 += gsz) {
             const uint64_t g = std::min(gsz, m1 - g0);

@@ -151,3 +151,41 @@ def s3_etag(part_md5s):
     buf = ctypes.create_string_buffer(64)
     lib().gho_s3_etag(_ptr(a), a.size // 16, buf)
     return buf.value.decode()
+
+
+# ---- OpenSSL (SHA-NI) baseline: oracle/gh_openssl.c, optional -------------------------------------
+_ossl = None
+
+
+def openssl_lib():
+    """libgh_openssl.so or None when it could not be built (no OpenSSL headers)."""
+    global _ossl
+    if _ossl is None:
+        so = os.path.join(_HERE, "libgh_openssl.so")
+        src = os.path.join(_HERE, "gh_openssl.c")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+            subprocess.call(["make", "-s", "-C", _HERE, "-B", "libgh_openssl.so"])
+        if not os.path.exists(so):
+            _ossl = False
+        else:
+            L = ctypes.CDLL(so)
+            L.gho_openssl_hash_msgs_mt.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64,
+                                                   ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+            L.gho_openssl_hash_msgs_mt.restype = ctypes.c_int
+            _ossl = L
+    return _ossl or None
+
+
+def openssl_hash_msgs(algs, data, msg_len, nthreads=1):
+    """{alg: digests} for every bit of `algs`, computed by OpenSSL EVP on `nthreads` threads."""
+    L = openssl_lib()
+    if L is None:
+        raise RuntimeError("libgh_openssl.so is not available")
+    a = _as_u8(data)
+    n = count(a.size, msg_len)
+    outs = {alg: np.empty((n, DIGEST_LEN[alg]), dtype=np.uint8) for alg in (SHA1, MD5, SHA256) if algs & alg}
+    if n:
+        L.gho_openssl_hash_msgs_mt(algs, _ptr(a), a.size, msg_len, _ptr(outs[SHA1]) if SHA1 in outs else None,
+                                   _ptr(outs[MD5]) if MD5 in outs else None, _ptr(outs[SHA256]) if SHA256 in outs else None,
+                                   nthreads)
+    return outs

@@ -120,3 +120,16 @@ def test_verify_bitmap_and_cfg5_rule():
     # the rule itself: ~1 % of indices selected, deterministic
     hits = sum(oracle.cfg5_corruption(i, L)[0] for i in range(20000))
     assert 120 <= hits <= 280
+
+
+def test_openssl_baseline_agrees_with_the_oracle():
+    """oracle/gh_openssl.c (the second CPU baseline, OpenSSL EVP) against the scalar port on ragged batches."""
+    import numpy as np
+    import pytest
+    if oracle.openssl_lib() is None:
+        pytest.skip("OpenSSL headers not present: libgh_openssl.so not built")
+    data = oracle.gen(17, 5, 3 * 65536 + 4321)
+    for L in (1, 55, 64, 1000, 16384, 65536, data.size + 5):
+        got = oracle.openssl_hash_msgs(7, data[: min(data.size, 4000 * L)], L, 3)
+        for a in (oracle.SHA1, oracle.MD5, oracle.SHA256):
+            assert np.array_equal(got[a], oracle.hash_msgs(a, data[: min(data.size, 4000 * L)], L, 2)), (a, L)

@@ -62,6 +62,27 @@ def cpu_sha1(host_arr, L, sample):
     return round(s / (time.perf_counter() - t0) / 1e9, 2)
 
 
+def openssl_rate(host_arr, L, sample, algs=("sha1",)):
+    """OpenSSL EVP (SHA-NI for SHA-1 / SHA-256 where the CPU has it) on all host threads through the C
+    harness oracle/gh_openssl.c: the upper bound of the two CPU figures (the oracle port is the lower)."""
+    s = min(sample, host_arr.size) // L * L
+    mask = sum({"sha1": 1, "md5": 2, "sha256": 4}[a] for a in algs)
+    t0 = time.perf_counter()
+    oracle.openssl_hash_msgs(mask, host_arr[:s], L, threads)
+    return round(s / (time.perf_counter() - t0) / 1e9, 2)
+
+
+def alu_frac(kernel, n_msgs, msg_len, ms):
+    """Fraction of the INT32 ALU pipes' issue capacity (148 SMs x 64 lanes x 1 965 MHz) the launch used:
+    blocks/s x ALU instructions per block from the shipped SASS (bench.py's roofline formula)."""
+    import bench
+    mix = bench.alu_instructions_per_block(kernel)
+    if not mix:
+        return None
+    blocks = n_msgs * ((msg_len + 9 + 63) // 64)
+    return round(blocks / (ms / 1e3) * mix["alu"] / (148 * 64 * 1.965e9), 3)
+
+
 def sha1_config(name, seed, file_sizes, L, corrupt_cfg5=False):
     total = sum(file_sizes)
     n = (total + L - 1) // L
@@ -101,6 +122,8 @@ def sha1_config(name, seed, file_sizes, L, corrupt_cfg5=False):
     assert got_bad == bad, (name, got_bad[:5], bad[:5])
     res["kernel_only_GBps"] = round(total / ms / 1e6, 1)
     res["kernel_ms"] = round(ms, 3)
+    res["kernel"] = gpuhash.last_kernel()
+    res["alu_pipe_frac"] = alu_frac(res["kernel"], n, L, ms)
     # end to end from pinned host spans (one span per file)
     host = to_host(d, total)
     files, o = [], 0
@@ -126,6 +149,7 @@ def sha1_config(name, seed, file_sizes, L, corrupt_cfg5=False):
         res["bitmap_identical_to_cpu"] = True
         res["n_bad"] = nbad
     res["cpu_port_GBps"] = cpu_sha1(host.array, L, 8 << 30)
+    res["cpu_openssl_GBps"] = openssl_rate(host.array, L, 8 << 30)
     host.free()
     del d
     torch.cuda.empty_cache()
@@ -151,6 +175,7 @@ if not only or "3" in only:
     for algos, nm in ((gpuhash.MD5 | gpuhash.SHA256, "fused"), (gpuhash.MD5, "md5"), (gpuhash.SHA256, "sha256")):
         ms = ev_time(lambda: ctx.hash_parts_device(d.data_ptr(), total, P, algos, None, md5.data_ptr(), sha.data_ptr(), stream=sp), reps=1)
         res["kernel_only_%s_GBps" % nm] = round(total / ms / 1e6, 2)
+        res["kernel_%s" % nm] = gpuhash.last_kernel()
     m = md5.cpu().numpy().reshape(n, 16)
     s = sha.cpu().numpy().reshape(n, 32)
     for i in (0, n - 1):
@@ -172,10 +197,50 @@ if not only or "3" in only:
     oracle.hash_msgs(oracle.MD5, host.array[:smp], P, threads)
     oracle.hash_msgs(oracle.SHA256, host.array[:smp], P, threads)
     res["cpu_port_md5_plus_sha256_GBps"] = round(smp / (time.perf_counter() - t0) / 1e9, 2)
+    res["cpu_openssl_md5_plus_sha256_GBps"] = openssl_rate(host.array, P, total, ("md5", "sha256"))
     host.free()
     out["config3_20GiB_64MiB_md5_sha256"] = res
     print("config3", json.dumps(res), flush=True)
+if not only or "chunks" in only:
+    # what the reference's exact upload call hashes client-side over plain HTTP (uploader.go:32-35, :89):
+    # SHA-256 of every 64 KiB chunk of the body (streaming SigV4) -- 327 680 independent messages per 20 GiB
+    C, total = 64 << 10, 20 << 30
+    n = total // C
+    d = torch.empty(total, dtype=torch.uint8, device="cuda")
+    ctx.generate(d.data_ptr(), 3, 0, total, stream=sp)
+    sha = torch.zeros(n * 32, dtype=torch.uint8, device="cuda")
+    ms = ev_time(lambda: ctx.hash_parts_device(d.data_ptr(), total, C, gpuhash.SHA256, None, None, sha.data_ptr(), stream=sp))
+    res = {"chunks": n, "bytes": total, "chunk_len": C, "kernel_only_GBps": round(total / ms / 1e6, 1), "kernel_ms": round(ms, 3),
+           "kernel": gpuhash.last_kernel()}
+    res["alu_pipe_frac"] = alu_frac(res["kernel"], n, C, ms)
+    res["frac_of_sha256_alu_bound_1072GBps"] = round(res["kernel_only_GBps"] / 1072.0, 3)
+    s = sha.cpu().numpy().reshape(n, 32)
+    host = to_host(d, total)
+    for off in (0, total - (1 << 30)):
+        want = oracle.hash_msgs(oracle.SHA256, host.array[off:off + (1 << 30)], C, threads)
+        assert np.array_equal(s[off // C:(off + (1 << 30)) // C], want)
+    r = {}
+
+    def e2ec():
+        r["v"] = ctx.HashParts([host.array], C, gpuhash.SHA256)
+    dt = wall(e2ec, reps=2)
+    assert np.array_equal(r["v"][gpuhash.SHA256], s)
+    res["e2e_GBps"] = round(total / dt / 1e9, 2)
+    res["e2e_kernel_ms"] = round(ctx.stats().kernel_ms, 1)
+    # the chunk signatures chain in order (each signs the previous signature + this chunk's hex digest):
+    # the signer needs lowercase hex, chunk order -- exactly the rows of the output, hexlified
+    res["first_chunk_hex"] = s[0].tobytes().hex()
+    smp = 4 << 30
+    t0 = time.perf_counter()
+    oracle.hash_msgs(oracle.SHA256, host.array[:smp], C, threads)
+    res["cpu_port_GBps"] = round(smp / (time.perf_counter() - t0) / 1e9, 2)
+    res["cpu_openssl_GBps"] = openssl_rate(host.array, C, 8 << 30, ("sha256",))
+    host.free()
+    del d
+    torch.cuda.empty_cache()
+    out["sha256_64KiB_chunks_20GiB"] = res
+    print("chunks", json.dumps(res), flush=True)
 
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-json.dump(out, open(os.path.join(ROOT, "gpurun_out", "configs.json"), "w"), indent=1)
+json.dump(out, open(os.path.join(ROOT, "gpurun_out", os.environ.get("CONFIGS_OUT", "configs.json")), "w"), indent=1)
 print("done")
