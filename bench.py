@@ -499,11 +499,12 @@ def main():
         print("bench.py: SASS instruction count unavailable: %r" % (e,), file=sys.stderr)
     blocks_per_launch = n_pieces * ((PIECE_LEN + 9 + 63) // 64)
     clock_mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965
+    same_kernel = prof.get("kernel", "?").split("<")[0] == kernel_name.split("<")[0]  # DRAM traffic does not depend on the template arguments
     roofline = {"kernel": kernel_name, "algorithmic_bytes_per_launch": total, "launch_ms": round(launch_ms, 3),
                 "hbm": {"achieved": round(hbm_achieved, 2), "peak": hbm_peak, "unit": "GB/s", "frac": round(hbm_achieved / hbm_peak, 4),
                         "peak_source": hbm_src},
-                "traffic": prof.get("dram_bytes_per_launch") if prof.get("kernel") == kernel_name else None,
-                "traffic_source": prof.get("source") if prof.get("kernel") == kernel_name else None}
+                "traffic": prof.get("dram_bytes_per_launch") if same_kernel else None,
+                "traffic_source": prof.get("source") if same_kernel else None}
     if mix:
         achieved = blocks_per_launch / (launch_ms / 1e3) * mix["alu"] / 1e12       # T thread-instructions / s
         peak = sms * 64 * clock_mhz * 1e6 / 1e12

@@ -697,19 +697,29 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 // Every (chain, buffer) has exactly one producer warp and one consumer warp, so the full/empty
 // mbarrier pairs never have two waiters a phase apart; each S warp owns the two TMA stages of its
 // batch parity and is their only reader, so the tile ring needs no "empty" barrier.
+#ifndef GH_TRIO_RATIO3
+#define GH_TRIO_RATIO3 2  // S_a : S_b share in the three-chains-per-CTA layout (2:1 measured +5 % over 1:1 at config 2)
+#endif
 #ifndef GH_TRIO_DEBUG
 #define GH_TRIO_DEBUG 0  // measurement builds only: 1 = rounds warps idle, 2 = schedule warps idle (digests are then wrong)
 #endif
 constexpr int kTrioMaxChains = 3;
 constexpr int kTrioH = 2;          // blocks per hand-off batch = one TMA tile row of 128 bytes per message
-constexpr int kTrioStages = 4;     // per chain: two per schedule warp
 constexpr uint32_t kTrioWkBlock = 80 * 32 * 4;                       // [t/4][lane][4]
-constexpr uint32_t kTrioTilesPerChain = kTrioStages * kTileBytes;    // 16 KiB
-constexpr uint32_t kTrioWkPerChain = 2 * kTrioH * kTrioWkBlock;      // 40 KiB: one buffer per schedule warp
-constexpr uint32_t kTrioBarsPerChain = 8 * (kTrioStages + 4);
-__host__ __device__ constexpr uint32_t trio_smem(int chains) {
-    return chains * (kTrioTilesPerChain + kTrioWkPerChain + kTrioBarsPerChain) + 64;
-}
+// RATIO = how many hand-off batches S_a takes for each one S_b takes. S_b shares its sub-partition with
+// R in the three-chain layout, S_a's sit together on the fourth: 2:1 evens the ALU load out (R 650 +
+// S_b 142 issue clocks per block-step against 3 x 284 on the S_a sub-partition; 1:1 is 863 against 639).
+// Batch q goes to WK buffer q % (RATIO+1); S_b owns the last buffer, S_a the others; TMA stage q % stages
+// with stages a multiple of RATIO+1, so every buffer and every stage has exactly one producer warp.
+template <int RATIO>
+struct TrioCfg {
+    static constexpr uint32_t kBufs = RATIO + 1;
+    static constexpr uint32_t kStages = RATIO == 1 ? 4 : RATIO + 1;
+    static constexpr uint32_t kTilesPerChain = kStages * kTileBytes;
+    static constexpr uint32_t kWkPerChain = kBufs * kTrioH * kTrioWkBlock;
+    static constexpr uint32_t kBarsPerChain = 8 * (kStages + 2 * kBufs);
+    __host__ __device__ static constexpr uint32_t smem(int chains) { return chains * (kTilesPerChain + kWkPerChain + kBarsPerChain) + 64; }
+};
 __host__ __device__ constexpr int trio_warps(int chains) { return chains == 1 ? 3 : chains == 2 ? 8 : 12; }
 
 // role of warp w in a CTA of `chains` chains: 0 = rounds, 1 = schedule (even batches), 2 = schedule (odd), 3 = none
@@ -735,9 +745,13 @@ __device__ __forceinline__ void trio_role(uint32_t w, uint32_t chains, uint32_t*
     }
 }
 
+template <int RATIO>
 __global__ void __launch_bounds__(32 * 12)
 gh_hash_trio(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     extern __shared__ __align__(1024) uint8_t smem[];
+    using Cfg = TrioCfg<RATIO>;
+    constexpr uint32_t kBufs = Cfg::kBufs, kTrioStages = Cfg::kStages;
+    constexpr uint32_t kTrioTilesPerChain = Cfg::kTilesPerChain, kTrioWkPerChain = Cfg::kWkPerChain, kTrioBarsPerChain = Cfg::kBarsPerChain;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t chains = job.chains_per_cta;
     uint32_t role, ci;
@@ -756,38 +770,40 @@ gh_hash_trio(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     const uint32_t tiles = base + ci * kTrioTilesPerChain;
     const uint32_t wk = base + chains * kTrioTilesPerChain + ci * kTrioWkPerChain;
     const uint32_t bars = base + chains * (kTrioTilesPerChain + kTrioWkPerChain) + ci * kTrioBarsPerChain;
-    const uint32_t tile_full = bars, w_full = bars + 8 * kTrioStages, w_empty = w_full + 16;
+    const uint32_t tile_full = bars, w_full = bars + 8 * kTrioStages, w_empty = w_full + 8 * kBufs;
     if (threadIdx.x == 0) {
         const uint32_t b0 = base + chains * (kTrioTilesPerChain + kTrioWkPerChain);
-        for (uint32_t k = 0; k < chains * (kTrioStages + 4); k++) mbar_init(b0 + 8 * k, 1);
+        for (uint32_t k = 0; k < chains * (kTrioStages + 2 * kBufs); k++) mbar_init(b0 + 8 * k, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();  // the only CTA-wide barrier
     if (role == 3 || ci >= n_mw) return;
 
     if (role != 0) {
-        // ------------------------------------------------------------------ schedule warp of parity p
-        const uint32_t p = role - 1;  // batches q = p, p+2, p+4 ...; WK buffer p; TMA stages p and p+2
+        // ------------------------------------------------------------------ schedule warp
+        // S_b (role 2) takes the batches q = kBufs-1 (mod kBufs), S_a (role 1) all others; a batch's WK buffer
+        // is q % kBufs and its TMA stage q % kTrioStages, both owned by the warp that owns the batch.
+        const bool is_b = role == 2;
+        auto mine = [&](uint32_t q) { return ((q % kBufs) == kBufs - 1) == is_b; };
         const uint32_t sw = lane & 7u;
         const uint32_t row0 = static_cast<uint32_t>(job.first_msg + (mw0 + ci) * 32u);
         const uint32_t row_base = tiles + lane * kTileRowBytes;
-        const uint32_t wk0 = wk + p * kTrioH * kTrioWkBlock + lane * 16;
         auto issue = [&](uint32_t q) {  // batch q = bytes [128 q, 128 q + 128) of every message
             const uint32_t st = q % kTrioStages;
             mbar_arrive_expect_tx(tile_full + 8 * st, kTileBytes);
             tma_load_box(tiles + st * kTileBytes, &tmap, q * (kTileRowBytes / 4), row0, tile_full + 8 * st);
         };
-        if (lane == 0) {
-            if (p < n_batches) issue(p);
-            if (p + 2 < n_batches) issue(p + 2);
-        }
-        uint32_t use = 0;
+        if (lane == 0)
+            for (uint32_t q = 0; q < kTrioStages && q < n_batches; q++)
+                if (mine(q)) issue(q);
 #pragma unroll 1
-        for (uint32_t q = p; q < n_batches; q += 2, use++) {
-            const uint32_t st = q % kTrioStages;
+        for (uint32_t q = 0; q < n_batches; q++) {
+            if (!mine(q)) continue;
+            const uint32_t st = q % kTrioStages, buf = q % kBufs, use = q / kBufs;
             mbar_wait(tile_full + 8 * st, (q / kTrioStages) & 1u);
-            if (use) mbar_wait(w_empty + 8 * p, (use - 1) & 1u);  // R has drained this warp's buffer
+            if (use) mbar_wait(w_empty + 8 * buf, (use - 1) & 1u);  // R has drained this buffer
             const uint32_t nb = min(static_cast<uint32_t>(kTrioH), n_blocks - q * kTrioH);
+            const uint32_t wk0 = wk + buf * kTrioH * kTrioWkBlock + lane * 16;
 #pragma unroll 1
             for (uint32_t j = 0; j < nb; j++) {
 #if GH_TRIO_DEBUG != 2
@@ -800,7 +816,7 @@ gh_hash_trio(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
             }
             __syncwarp();  // every lane's stores and tile reads precede lane 0's release-arrive / re-issue
             if (lane == 0) {
-                mbar_arrive1(w_full + 8 * p);
+                mbar_arrive1(w_full + 8 * buf);
                 if (q + kTrioStages < n_batches) issue(q + kTrioStages);
             }
         }
@@ -825,8 +841,8 @@ gh_hash_trio(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
     else L.load(job.state, job.n_msgs, m);
 #pragma unroll 1
     for (uint32_t q = 0; q < n_batches; q++) {
-        const uint32_t p = q & 1u;
-        mbar_wait(w_full + 8 * p, (q >> 1) & 1u);
+        const uint32_t p = q % kBufs;
+        mbar_wait(w_full + 8 * p, (q / kBufs) & 1u);
         const uint32_t wk0 = wk + p * kTrioH * kTrioWkBlock + lane * 16;
 #pragma unroll 1
         for (uint32_t j = 0; j < kTrioH && q * kTrioH + j < n_blocks; j++)
@@ -943,6 +959,13 @@ int trio_max_warps_per_sm() {
     static const int v = env_int("GPUHASH_TRIO_WARPS_PER_SM", kTrioMaxChains);
     return v;
 }
+// Share of the schedule work between a chain's two schedule warps (S_a : S_b). GPUHASH_TRIO_RATIO=1|2
+// forces it; default per layout (measured, profiles/r02_ab_sha1_kernels.jsonl).
+int trio_ratio(int chains) {
+    static const int v = env_int("GPUHASH_TRIO_RATIO", 0);
+    if (v == 1 || v == 2) return v;
+    return chains == 3 ? GH_TRIO_RATIO3 : 1;
+}
 int forced_tps() {
     static const int v = env_int("GPUHASH_TPS", 0);
     return v;
@@ -993,8 +1016,11 @@ cudaError_t launch_trio(const GhJob& job_in, uint64_t count, int chains, const C
     const uint64_t n_mw = (count + 31) / 32;
     const uint64_t nblocks = (n_mw + chains - 1) / chains;
     if (nblocks > 0x7fffffffull) return cudaErrorInvalidValue;
-    gh_hash_trio<<<dim3(static_cast<unsigned>(nblocks)), dim3(32 * trio_warps(chains)), trio_smem(chains), stream>>>(tmap, job);
-    g_last_kernel = "gh_hash_trio";
+    if (trio_ratio(chains) == 2)
+        gh_hash_trio<2><<<dim3(static_cast<unsigned>(nblocks)), dim3(32 * trio_warps(chains)), TrioCfg<2>::smem(chains), stream>>>(tmap, job);
+    else
+        gh_hash_trio<1><<<dim3(static_cast<unsigned>(nblocks)), dim3(32 * trio_warps(chains)), TrioCfg<1>::smem(chains), stream>>>(tmap, job);
+    g_last_kernel = trio_ratio(chains) == 2 ? "gh_hash_trio<2>" : "gh_hash_trio<1>";
     return cudaGetLastError();
 }
 
@@ -1126,9 +1152,13 @@ cudaError_t gh_kernels_init_device() {
     if ((e = init_split<GH_SHA1, false>()) != cudaSuccess) return e;
     if ((e = init_split<GH_SHA256, false>()) != cudaSuccess) return e;
     if ((e = init_split<GH_SHA256, true>()) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(gh_hash_trio, cudaFuncAttributeMaxDynamicSharedMemorySize, trio_smem(kTrioMaxChains))) != cudaSuccess)
+    if ((e = cudaFuncSetAttribute(gh_hash_trio<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrioCfg<1>::smem(kTrioMaxChains))) != cudaSuccess)
         return e;
-    if ((e = cudaFuncSetAttribute(gh_hash_trio, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess)
+    if ((e = cudaFuncSetAttribute(gh_hash_trio<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess)
+        return e;
+    if ((e = cudaFuncSetAttribute(gh_hash_trio<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrioCfg<2>::smem(kTrioMaxChains))) != cudaSuccess)
+        return e;
+    if ((e = cudaFuncSetAttribute(gh_hash_trio<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess)
         return e;
     return encode_tiled() ? cudaSuccess : cudaErrorNotSupported;
 }

@@ -37,7 +37,7 @@ def test_trio_shapes_device_resident(gh, L, last):
     dig = torch.zeros(n * 20, dtype=torch.uint8, device="cuda")
     gh.verify_pieces_device(d.data_ptr(), total, L, None, dig.data_ptr(), None)
     if os.environ.get("GPUHASH_TRIO_WARPS_PER_SM") != "0":
-        assert gpuhash.last_kernel() == "gh_hash_trio"  # the shape really is routed to the kernel under test
+        assert gpuhash.last_kernel().startswith("gh_hash_trio")  # the shape really is routed to the kernel under test
     want = oracle.hash_msgs(oracle.SHA1, host, L, 8)
     assert np.array_equal(dig.cpu().numpy().reshape(n, 20), want)
     # verification: corrupt pieces at warp / CTA / bitmap-word edges, bitmap and digests on the device
