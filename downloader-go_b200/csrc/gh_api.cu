@@ -1149,6 +1149,8 @@ struct gh_stream {
     bool want_ok = false, acquired = false;
     uint64_t o_sha1 = 0, o_md5 = 0, o_sha256 = 0, o_exp = 0, ok_words = 0;
     uint64_t cap = 0;  // bytes the acquired window must receive
+    struct Win { int dev; uint64_t first, count; };
+    std::vector<Win> wins;  // which device hashed which messages (windows go round the context's devices)
 };
 
 static void stream_release(gh_stream* st) {
@@ -1158,6 +1160,16 @@ static void stream_release(gh_stream* st) {
         st->c->stream_open = false;
     }
     delete st;
+}
+
+// window w of a stream lives on device w % n_devices, in that device's ring slot (w / n_devices) % slots
+static Device& stream_dev(gh_stream* st, uint64_t w) { return st->c->devs[w % st->c->devs.size()]; }
+static Slot& stream_slot(gh_stream* st, uint64_t w) {
+    Device& d = stream_dev(st, w);
+    return d.slots[(w / st->c->devs.size()) % d.slots.size()];
+}
+static void stream_drain_all(gh_ctx* c) {
+    for (auto& d : c->devs) drain_device(d);
 }
 
 int gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len, const uint8_t* expected,
@@ -1171,8 +1183,6 @@ int gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len,
     if (!(algos & 7) || (algos & ~7)) return fail(ctx, GH_EINVAL, "bad algos mask");
     if (msg_len > ctx->slot_bytes)
         return fail(ctx, GH_ERANGE, "message longer than a ring slot: use gh_hash_parts / gh_hash_file_parts, which interleave");
-    Device& d = ctx->devs[0];
-    GH_CUDA(ctx, cudaSetDevice(d.ordinal));
     gh_stream* st = new gh_stream();
     st->c = ctx;
     st->algos = algos;
@@ -1189,24 +1199,29 @@ int gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len,
     st->o_exp = st->o_sha256 + al(32 * n);
     st->ok_words = (n + 31) / 32;
     const uint64_t out_bytes = st->o_exp + al(20 * n);
-    int rc;
-    if ((rc = grow(ctx, &d.d_out, &d.d_out_cap, out_bytes)) || (rc = grow(ctx, &d.h_out, &d.h_out_cap, out_bytes, true)) ||
-        (rc = grow(ctx, &d.d_ok, &d.d_ok_cap, (st->ok_words + 1) * 4))) {
-        delete st;
-        return rc;
-    }
-    if (st->want_ok) {
-        memcpy(d.h_out + st->o_exp, expected, 20 * st->n);
-        cudaError_t e = cudaMemcpyAsync(d.d_out + st->o_exp, d.h_out + st->o_exp, 20 * st->n, cudaMemcpyHostToDevice, d.stream);
-        if (e == cudaSuccess) e = cudaMemsetAsync(d.d_ok, 0, (st->ok_words + 1) * 4, d.stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);  // h_out is reused for results later
-        if (e != cudaSuccess) {
-            delete st;
-            return cuda_fail(ctx, e, "gh_stream_open");
+    // every device gets result arrays for the whole stream (digests are 20-68 bytes per message) and the
+    // expected digests; at finish each window's slice is read back from the device that hashed it
+    for (auto& d : ctx->devs) {
+        int rc = GH_OK;
+        cudaError_t e = cudaSetDevice(d.ordinal);
+        if (e != cudaSuccess) rc = cuda_fail(ctx, e, "cudaSetDevice");
+        if (!rc) rc = grow(ctx, &d.d_out, &d.d_out_cap, out_bytes);
+        if (!rc) rc = grow(ctx, &d.h_out, &d.h_out_cap, out_bytes, true);
+        if (!rc) rc = grow(ctx, &d.d_ok, &d.d_ok_cap, (st->ok_words + 1) * 4);
+        if (!rc && st->want_ok) {
+            memcpy(d.h_out + st->o_exp, expected, 20 * st->n);
+            e = cudaMemcpyAsync(d.d_out + st->o_exp, d.h_out + st->o_exp, 20 * st->n, cudaMemcpyHostToDevice, d.stream);
+            if (e == cudaSuccess) e = cudaMemsetAsync(d.d_ok, 0, (st->ok_words + 1) * 4, d.stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);  // h_out is reused for results later
+            if (e != cudaSuccess) rc = cuda_fail(ctx, e, "gh_stream_open");
         }
+        if (rc) {
+            delete st;
+            return rc;
+        }
+        for (auto& sl : d.slots) sl.in_use = false;
+        d.ev_used = 0;
     }
-    for (auto& sl : d.slots) sl.in_use = false;
-    d.ev_used = 0;
     ctx->stream_open = true;
     *out = st;
     return GH_OK;
@@ -1222,10 +1237,10 @@ int gh_stream_acquire(gh_stream* st, void** buf, uint64_t* cap) {
         *cap = 0;
         return GH_OK;  // everything has been fed
     }
-    Device& d = c->devs[0];
+    Device& d = stream_dev(st, st->window);
     GH_CUDA(c, cudaSetDevice(d.ordinal));
-    Slot& s = d.slots[st->window % d.slots.size()];
-    if (!s.h_pin) GH_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256));
+    Slot& s = stream_slot(st, st->window);
+    if (!s.h_pin) GH_CUDA(c, cudaHostAlloc(reinterpret_cast<void**>(&s.h_pin), c->slot_bytes + 256, cudaHostAllocPortable));
     if (s.h2d_pending) {  // the DMA that last read this pinned buffer must have drained
         GH_CUDA(c, cudaEventSynchronize(s.h2d_done));
         s.h2d_pending = false;
@@ -1245,9 +1260,9 @@ int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
     std::lock_guard<std::mutex> g(c->mu);
     if (!st->acquired) return fail(c, GH_EINVAL, "gh_stream_submit without gh_stream_acquire");
     if (n_bytes != st->cap) return fail(c, GH_EINVAL, "gh_stream_submit: a window must be filled completely (cap bytes)");
-    Device& d = c->devs[0];
+    Device& d = stream_dev(st, st->window);
     GH_CUDA(c, cudaSetDevice(d.ordinal));
-    Slot& s = d.slots[st->window % d.slots.size()];
+    Slot& s = stream_slot(st, st->window);
     int rc = slot_begin(c, s);
     StagedRuns staged;
     staged.add(0, n_bytes);
@@ -1257,7 +1272,7 @@ int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
     }
     if (!rc) rc = flush_staged(c, s, staged);
     if (rc) {  // nothing of this stream may still be running when the caller sees the error and aborts
-        drain_device(d);
+        stream_drain_all(c);
         return rc;
     }
     c->h2d += n_bytes;
@@ -1279,9 +1294,10 @@ int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
         j.ok_base = rel;
     }
     if ((rc = slot_launch(c, d, s, st->algos, j))) {
-        drain_device(d);
+        stream_drain_all(c);
         return rc;
     }
+    st->wins.push_back({static_cast<int>(st->window % c->devs.size()), rel, k});
     st->next_msg += k;
     st->fed += n_bytes;
     st->window++;
@@ -1296,36 +1312,50 @@ int gh_stream_finish(gh_stream* st, uint8_t* sha1_out, uint8_t* md5_out, uint8_t
     int rc = GH_OK;
     {
         std::lock_guard<std::mutex> g(c->mu);
-        Device& d = c->devs[0];
         if (st->next_msg != st->n || st->acquired) {
             rc = fail(c, GH_EINVAL, "gh_stream_finish before every window was submitted (use gh_stream_abort to give up)");
-        } else if (cudaSetDevice(d.ordinal) != cudaSuccess) {
-            rc = GH_ECUDA;
         } else {
             const uint64_t n = st->n;
-            cudaError_t e = cudaSuccess;
             struct { int alg; uint64_t off; uint8_t* dst; int dl; } outs[3] = {
                 {GH_SHA1, st->o_sha1, sha1_out, 20}, {GH_MD5, st->o_md5, md5_out, 16}, {GH_SHA256, st->o_sha256, sha256_out, 32}};
-            for (auto& o : outs)
-                if ((st->algos & o.alg) && o.dst && n && e == cudaSuccess) {
-                    e = cudaMemcpyAsync(d.h_out + o.off, d.d_out + o.off, o.dl * n, cudaMemcpyDeviceToHost, d.stream);
-                    c->d2h += o.dl * n;
-                }
-            uint32_t* h_ok = reinterpret_cast<uint32_t*>(d.h_out + st->o_exp);
-            if (st->want_ok && n && e == cudaSuccess)
-                e = cudaMemcpyAsync(h_ok, d.d_ok, st->ok_words * 4, cudaMemcpyDeviceToHost, d.stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);
-            for (auto& sl : d.slots) sl.h2d_pending = false;
+            cudaError_t e = cudaSuccess;
+            // queue every window's slices (and every device's bitmap words) for read-back, then wait per device
+            for (const auto& w : st->wins) {
+                Device& d = c->devs[w.dev];
+                if (e == cudaSuccess) e = cudaSetDevice(d.ordinal);
+                for (auto& o : outs)
+                    if ((st->algos & o.alg) && o.dst && e == cudaSuccess) {
+                        e = cudaMemcpyAsync(d.h_out + o.off + o.dl * w.first, d.d_out + o.off + o.dl * w.first, o.dl * w.count,
+                                            cudaMemcpyDeviceToHost, d.stream);
+                        c->d2h += o.dl * w.count;
+                    }
+            }
+            for (auto& d : c->devs) {
+                if (e == cudaSuccess) e = cudaSetDevice(d.ordinal);
+                uint32_t* h_ok = reinterpret_cast<uint32_t*>(d.h_out + st->o_exp);
+                if (st->want_ok && n && e == cudaSuccess)
+                    e = cudaMemcpyAsync(h_ok, d.d_ok, st->ok_words * 4, cudaMemcpyDeviceToHost, d.stream);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(d.stream);
+                for (auto& sl : d.slots) sl.h2d_pending = false;
+            }
             if (e != cudaSuccess) {
                 rc = cuda_fail(c, e, "gh_stream_finish");
+                stream_drain_all(c);
             } else {
-                for (auto& o : outs)
-                    if ((st->algos & o.alg) && o.dst && n) memcpy(o.dst, d.h_out + o.off, o.dl * n);
+                for (const auto& w : st->wins)
+                    for (auto& o : outs)
+                        if ((st->algos & o.alg) && o.dst)
+                            memcpy(o.dst + o.dl * w.first, c->devs[w.dev].h_out + o.off + o.dl * w.first, o.dl * w.count);
                 if (n_bad_out) *n_bad_out = 0;
                 if (ok_bitmap_out && n) {
                     memset(ok_bitmap_out, 0, ((n + 63) / 64) * 8);
                     if (st->want_ok) {
-                        memcpy(ok_bitmap_out, h_ok, st->ok_words * 4);
+                        // a device's bitmap holds 1s only for pieces it hashed itself: OR them together
+                        uint32_t* dst = reinterpret_cast<uint32_t*>(ok_bitmap_out);
+                        for (auto& d : c->devs) {
+                            const uint32_t* h_ok = reinterpret_cast<const uint32_t*>(d.h_out + st->o_exp);
+                            for (uint64_t k = 0; k < st->ok_words; k++) dst[k] |= h_ok[k];
+                        }
                         uint64_t good = 0;
                         for (uint64_t w = 0; w < (n + 63) / 64; w++) good += __builtin_popcountll(ok_bitmap_out[w]);
                         if (n_bad_out) *n_bad_out = n - good;
@@ -1343,9 +1373,7 @@ void gh_stream_abort(gh_stream* st) {
     gh_ctx* c = st->c;
     {
         std::lock_guard<std::mutex> g(c->mu);
-        Device& d = c->devs[0];
-        if (cudaSetDevice(d.ordinal) == cudaSuccess) cudaDeviceSynchronize();
-        for (auto& sl : d.slots) sl.h2d_pending = false;
+        stream_drain_all(c);
     }
     stream_release(st);
 }

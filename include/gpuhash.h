@@ -166,8 +166,10 @@ int gh_hash_file_parts(gh_ctx* ctx, const gh_file* files, size_t n_files, uint64
  *   abort   -> drop the stream
  * Messages longer than a ring slot are refused with GH_ERANGE (sequential feeding would leave one
  * chain per window; gh_hash_parts / gh_hash_file_parts interleave such messages instead). A context
- * carries one stream at a time and refuses one-shot calls while it is open. Uses the context's
- * first device. */
+ * carries one stream at a time and refuses one-shot calls while it is open. Windows go round the
+ * context's devices (window w on device w mod n_devices, each with its own pinned ring), so a feed
+ * that outruns one GPU's link spreads over all of them; finish gathers digests and bitmap from the
+ * devices that produced them. After an error from submit or finish the stream can only be aborted. */
 typedef struct gh_stream gh_stream;
 int  gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len, const uint8_t* expected,
                     gh_stream** out);

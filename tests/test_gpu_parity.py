@@ -444,6 +444,36 @@ def test_incremental_stream_feed():
         ctx.close()
 
 
+def test_incremental_stream_feed_over_all_devices():
+    """The same feed on a context over every visible device: windows go round the devices, digests
+    and the bitmap are gathered from whichever device hashed a piece (one GPU: the degenerate case)."""
+    ctx = gpuhash.Context(slot_bytes=1 << 20, slots=2)
+    try:
+        L = 16384
+        total = 1000 * L + 5  # 1001 pieces, 64 per window -> 16 windows
+        data = oracle.gen(16, 0, total)
+        expected = oracle.hash_msgs(oracle.SHA1, data, L, 4)
+        dirty = data.copy()
+        bad = [0, 63, 64, 127, 128, 500, 1000]
+        for i in bad:
+            dirty[i * L] ^= 2
+        st = ctx.Stream(gpuhash.SHA1 | gpuhash.SHA256, L, total, expected)
+        off = 0
+        while True:
+            buf = st.acquire()
+            if buf is None:
+                break
+            buf[:] = dirty[off:off + len(buf)]
+            off += len(buf)
+            st.submit()
+        bitmap, outs, nbad = st.finish()
+        assert nbad == len(bad) and [i for i, b in enumerate(_bits(bitmap, 1001)) if not b] == bad
+        assert np.array_equal(outs[gpuhash.SHA1], oracle.hash_msgs(oracle.SHA1, dirty, L, 4))
+        assert np.array_equal(outs[gpuhash.SHA256], oracle.hash_msgs(oracle.SHA256, dirty, L, 4))
+    finally:
+        ctx.close()
+
+
 @pytest.mark.parametrize("piece_len,total", [(1, 5000), (7, 7 * 3000 + 3), (63, 63 * 40), (64, 64), (4096, 100), (4096, 4096),
                                              (16, 16 * 33), (1 << 20, (1 << 20) + 1), (48, 48 * 1025)])
 def test_extreme_piece_shapes(gh, piece_len, total):
