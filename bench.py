@@ -295,27 +295,48 @@ def config4_strong(gpuhash, oracle, np, devices, threads):
     sizes = [(2 << 30) + 7919 * (k + 1) for k in range(24)]
     total = sum(sizes)
     n = (total + L - 1) // L
-    host = gpuhash.PinnedBuffer(total)
+    starts = [sum(sizes[:k]) for k in range(len(sizes))]
+    # host side: one pinned buffer per file (what a downloader that pins its file buffers would hold);
+    # if the driver refuses to pin that much next to the other ranks' contexts, pageable memory -- the
+    # library then stages through its own pinned ring -- and the line says so
+    bufs, host_mode = [], "pinned, one buffer per file"
     try:
-        parallel_gen(oracle, 4, 0, host.ptr, total, threads)
-        files, o = [], 0
-        for s in sizes:
-            files.append(host.array[o:o + s])
-            o += s
-        spans = gpuhash.SpanList(files)
+        for sz in sizes:
+            bufs.append(gpuhash.PinnedBuffer(sz))
+        arrays = [b.array for b in bufs]
+    except gpuhash.GpuHashError as e:
+        for b in bufs:
+            b.free()
+        bufs = []
+        arrays = [np.empty(sz, dtype=np.uint8) for sz in sizes]
+        host_mode = "pageable (pinned allocation refused: %s)" % e
+    try:
+        for a, st in zip(arrays, starts):
+            parallel_gen(oracle, 4, st, a.ctypes.data, a.size, threads)
+
+        def stream(lo, hi):  # bytes [lo, hi) of the concatenated stream
+            parts = []
+            for a, st in zip(arrays, starts):
+                x, y = max(lo, st), min(hi, st + a.size)
+                if x < y:
+                    parts.append(a[x - st:y - st])
+            return parts[0] if len(parts) == 1 else np.concatenate(parts)
+
+        spans = gpuhash.SpanList(arrays)
         ctx = gpuhash.Context(devices=list(devices))
         try:
             _, dig, _ = ctx.VerifyPieces(spans, L, None)
             expected = dig.copy()
-            check, off = {0, n - 1}, 0
-            for s in sizes[:3]:
-                off += s
-                check.add(off // L)  # pieces that straddle a file boundary
+            check = {0, n - 1}
+            for st in starts[1:4]:
+                check.add(st // L)  # pieces that straddle a file boundary
             for i in sorted(check):
                 lo, hi = i * L, min((i + 1) * L, total)
-                assert expected[i].tobytes() == oracle.digest(oracle.SHA1, host.array[lo:hi]), "config 4 piece %d" % i
+                assert expected[i].tobytes() == oracle.digest(oracle.SHA1, stream(lo, hi)), "config 4 piece %d" % i
             victim = 1234
-            host.array[victim * L + 99] ^= 1
+            pos = victim * L + 99
+            k = max(j for j, st in enumerate(starts) if st <= pos)
+            arrays[k][pos - starts[k]] ^= 1
             ctx.VerifyPieces(spans, L, expected)
             t0 = time.perf_counter()
             bitmap, dig, nbad = ctx.VerifyPieces(spans, L, expected)
@@ -323,12 +344,13 @@ def config4_strong(gpuhash, oracle, np, devices, threads):
             bad = [i for i in range(n) if not (int(bitmap[i >> 6]) >> (i & 63)) & 1]
             assert nbad == 1 and bad == [victim], (nbad, bad[:4])
             return {"e2e": round(total / dt / 1e9, 2), "unit": "GB/s", "ms": round(dt * 1e3, 1), "pieces": n, "files": len(sizes),
-                    "bytes": total, "n_bad": int(nbad), "devices": list(devices),
-                    "how": "one gh_ctx over all ranks' devices, pinned host spans (one per file), bitmap == {only piece %d bad}" % victim}
+                    "bytes": total, "n_bad": int(nbad), "devices": list(devices), "host_memory": host_mode,
+                    "how": "one gh_ctx over all ranks' devices, host spans one per file, bitmap == {only piece %d bad}" % victim}
         finally:
             ctx.close()
     finally:
-        host.free()
+        for b in bufs:
+            b.free()
 
 
 def main():
@@ -618,8 +640,8 @@ def main():
                 pass
             try:
                 c4 = config4_strong(gpuhash, oracle, np, devices, host_threads())
-            except MemoryError as e:
-                c4 = {"skipped": "host RAM: %r" % (e,)}
+            except (MemoryError, gpuhash.GpuHashError, AssertionError) as e:  # reported, never fatal for the weak-scaling line
+                c4 = {"failed": repr(e)[:300]}
         host_barrier()
 
     if rank == 0:

@@ -984,8 +984,16 @@ const char* gh_strerror(int status) {
     }
 }
 
+// context-free entry points (gh_host_alloc ...) leave their failure text here, per thread
+static thread_local std::string g_tls_error;
+static int tls_cuda_fail(cudaError_t e, const char* what) {
+    g_tls_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? GH_ENOMEM : GH_ECUDA;
+}
+
 const char* gh_last_error(gh_ctx* ctx) {
-    if (!ctx) return "";
+    if (!ctx) return g_tls_error.c_str();
     static thread_local std::string copy;  // valid until this thread's next gh_last_error call
     std::lock_guard<std::mutex> g(ctx->err_mu);
     copy = ctx->last_error;
@@ -1748,13 +1756,13 @@ int gh_generate_device(gh_ctx* ctx, int dev_index, void* d_out, uint64_t seed, u
 int gh_host_alloc(void** out, size_t bytes) {
     if (!out) return GH_EINVAL;
     cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
-    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? GH_ENOMEM : GH_ECUDA; }
+    if (e != cudaSuccess) return tls_cuda_fail(e, "cudaHostAlloc");
     return GH_OK;
 }
 int gh_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? GH_OK : GH_ECUDA; }
 int gh_host_register(void* p, size_t bytes) {
     cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
-    if (e != cudaSuccess) { cudaGetLastError(); return e == cudaErrorMemoryAllocation ? GH_ENOMEM : GH_ECUDA; }
+    if (e != cudaSuccess) return tls_cuda_fail(e, "cudaHostRegister");
     return GH_OK;
 }
 int gh_host_unregister(void* p) { return cudaHostUnregister(p) == cudaSuccess ? GH_OK : GH_ECUDA; }

@@ -243,7 +243,7 @@ class PinnedBuffer:
         p = ctypes.c_void_p()
         rc = load().gh_host_alloc(ctypes.byref(p), nbytes)
         if rc:
-            raise GpuHashError(rc, "gh_host_alloc(%d)" % nbytes)
+            raise GpuHashError(rc, "gh_host_alloc(%d)" % nbytes, load().gh_last_error(None).decode())
         self.ptr, self.nbytes = p.value, nbytes
         self.array = np.ctypeslib.as_array((ctypes.c_uint8 * max(nbytes, 1)).from_address(self.ptr))[:nbytes]
 

@@ -95,7 +95,9 @@ int         gh_create(gh_ctx** out, const gh_config* cfg /* NULL = defaults */);
 void        gh_destroy(gh_ctx* ctx);
 const char* gh_strerror(int status);
 const char* gh_last_error(gh_ctx* ctx);           /* detail of the last failure on this context; the pointer stays
-                                                     valid until the calling thread's next gh_last_error */
+                                                     valid until the calling thread's next gh_last_error. ctx == NULL:
+                                                     the calling thread's last failure in a context-free call
+                                                     (gh_host_alloc, gh_host_register) */
 int         gh_device_count(gh_ctx* ctx);
 int         gh_get_stats(gh_ctx* ctx, gh_stats* out);
 const char* gh_version(void);
