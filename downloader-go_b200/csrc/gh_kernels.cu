@@ -479,30 +479,15 @@ __device__ __forceinline__ void sha256_rounds(uint32_t (&s)[8], uint32_t wk_addr
 }
 
 // schedule warp: w = the block as big-endian-decoded words; writes WK[0..kWords) for its lane
-#ifndef GH_S_ROT_FMA
-#define GH_S_ROT_FMA 0  // n > 0: every n-th rotl1 of the SHA-1 schedule as IMAD.WIDE + add on the FMA pipe (A/B switch)
-#endif
-// rotl(x, 1) = (x << 1) + (x >> 31) = low + high word of x * 2; `two` is a kernel-parameter-derived 2 so
-// that ptxas keeps the multiply (IMAD.WIDE, FMA pipe) instead of turning it back into a shift
-__device__ __forceinline__ uint32_t rotl1_fma(uint32_t x, uint32_t two) {
-    uint32_t lo, hi;
-    asm("{ .reg .u64 p; mul.wide.u32 p, %2, %3; mov.b64 {%0, %1}, p; }" : "=r"(lo), "=r"(hi) : "r"(x), "r"(two));
-    return lo + hi;
-}
-
 template <int ALGO>
-__device__ __forceinline__ void expand_and_store(uint32_t (&w)[16], uint32_t wk_addr, uint32_t two = 2) {
+__device__ __forceinline__ void expand_and_store(uint32_t (&w)[16], uint32_t wk_addr) {
     uint32_t o[4];
     if constexpr (ALGO == GH_SHA1) {
 #pragma unroll
         for (int t = 0; t < 80; t++) {
             uint32_t wt;
             if (t < 16) wt = w[t];
-            else {
-                const uint32_t x = f_xor3(w[(t - 3) & 15], w[(t - 8) & 15], w[(t - 14) & 15]) ^ w[t & 15];
-                wt = (GH_S_ROT_FMA && (t % (GH_S_ROT_FMA ? GH_S_ROT_FMA : 1)) == 0) ? rotl1_fma(x, two) : rotl(x, 1);
-                w[t & 15] = wt;
-            }
+            else { wt = rotl(f_xor3(w[(t - 3) & 15], w[(t - 8) & 15], w[(t - 14) & 15]) ^ w[t & 15], 1); w[t & 15] = wt; }
             o[t & 3] = wt + sha1_k(t);
             if ((t & 3) == 3) sts128(wk_addr + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
         }
@@ -826,7 +811,7 @@ gh_hash_trio(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
                 lds_block(row_base + st * kTileBytes, j * 4u, sw, r);
 #pragma unroll
                 for (int k = 0; k < 16; k++) w[k] = bswap(r[k]);
-                expand_and_store<GH_SHA1>(w, wk0 + j * kTrioWkBlock, job.one + job.one);
+                expand_and_store<GH_SHA1>(w, wk0 + j * kTrioWkBlock);
 #endif
             }
             __syncwarp();  // every lane's stores and tile reads precede lane 0's release-arrive / re-issue
