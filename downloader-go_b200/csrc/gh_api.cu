@@ -1752,6 +1752,88 @@ int gh_generate_device(gh_ctx* ctx, int dev_index, void* d_out, uint64_t seed, u
     return GH_OK;
 }
 
+// ---- device placement ------------------------------------------------------------------------
+// End to end the path is bound by the host->device link, and on multi-GPU hosts several GPUs often
+// share one PCIe uplink (the 8xB200 box of DESIGN.md section 6: GPUs 0-3 together get 115 GB/s, GPUs
+// 0,2,4,6 get 213). Which n of the visible devices to use is therefore measured, not guessed: plain
+// pinned cudaMemcpyAsync on all devices of a candidate set at once, for the first n devices and for
+// an evenly strided set.
+namespace {
+double probe_h2d(const std::vector<int>& devs, double seconds) {
+    const size_t chunk = 128ull << 20;
+    const int n = static_cast<int>(devs.size());
+    std::vector<double> bytes(n, 0.0);
+    std::atomic<int> ready{0}, failed{0};
+    std::atomic<bool> go{false};
+    std::vector<std::thread> th;
+    std::chrono::steady_clock::time_point t0, t1;
+    for (int i = 0; i < n; i++)
+        th.emplace_back([&, i] {
+            void *h = nullptr, *d = nullptr;
+            cudaStream_t st = nullptr;
+            bool ok = cudaSetDevice(devs[i]) == cudaSuccess && cudaHostAlloc(&h, chunk, cudaHostAllocPortable) == cudaSuccess &&
+                      cudaMalloc(&d, chunk) == cudaSuccess && cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess;
+            if (ok) {
+                memset(h, 1, chunk);
+                ok = cudaMemcpyAsync(d, h, chunk, cudaMemcpyHostToDevice, st) == cudaSuccess && cudaStreamSynchronize(st) == cudaSuccess;
+            }
+            if (!ok) failed++;
+            ready++;
+            while (!go.load()) std::this_thread::yield();
+            const auto end = std::chrono::steady_clock::now() + std::chrono::duration<double>(seconds);
+            while (ok && std::chrono::steady_clock::now() < end) {
+                for (int k = 0; k < 4 && ok; k++) ok = cudaMemcpyAsync(d, h, chunk, cudaMemcpyHostToDevice, st) == cudaSuccess;
+                ok = ok && cudaStreamSynchronize(st) == cudaSuccess;
+                if (ok) bytes[i] += 4.0 * chunk;
+            }
+            if (st) cudaStreamDestroy(st);
+            if (d) cudaFree(d);
+            if (h) cudaFreeHost(h);
+            cudaGetLastError();
+        });
+    while (ready.load() < n) std::this_thread::yield();
+    t0 = std::chrono::steady_clock::now();
+    go = true;
+    for (auto& t : th) t.join();
+    t1 = std::chrono::steady_clock::now();
+    if (failed.load()) return -1.0;
+    double total = 0;
+    for (double b : bytes) total += b;
+    return total / std::chrono::duration<double>(t1 - t0).count() / 1e9;
+}
+}  // namespace
+
+int gh_suggest_devices(int n, int* devices_out, double* h2d_gbs_out) {
+    if (!devices_out || n <= 0) return GH_EINVAL;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return GH_ENODEVICE;
+    }
+    if (n > count) return GH_ENODEVICE;
+    std::vector<std::vector<int>> cands(1);
+    for (int i = 0; i < n; i++) cands[0].push_back(i);
+    if (count >= 2 * n) {
+        cands.emplace_back();
+        for (int i = 0; i < n; i++) cands[1].push_back(i * (count / n));
+    }
+    size_t best = 0;
+    double best_gbs = 0;
+    if (cands.size() > 1 || h2d_gbs_out) {
+        for (size_t c = 0; c < cands.size(); c++) {
+            const double g = probe_h2d(cands[c], 0.4);
+            if (g < 0) return GH_ECUDA;
+            if (g > best_gbs * 1.03) {  // a later candidate must be clearly better to displace the plain first-n choice
+                best_gbs = g;
+                best = c;
+            }
+        }
+    }
+    for (int i = 0; i < n; i++) devices_out[i] = cands[best][i];
+    if (h2d_gbs_out) *h2d_gbs_out = best_gbs;
+    return GH_OK;
+}
+
 // ---- memory helpers ------------------------------------------------------------------------
 int gh_host_alloc(void** out, size_t bytes) {
     if (!out) return GH_EINVAL;

@@ -562,3 +562,18 @@ func (b *Batcher) Close() {
 		b.b = nil
 	}
 }
+
+// SuggestDevices measures which n of the visible GPUs give the best aggregate host-to-device
+// bandwidth (GPUs behind one PCIe switch share its uplink) and returns their ordinals for New.
+func SuggestDevices(n int) ([]int, float64, error) {
+	devs := make([]C.int, n)
+	var gbs C.double
+	if rc := C.gh_suggest_devices(C.int(n), &devs[0], &gbs); rc != C.GH_OK {
+		return nil, 0, status(nil, rc, "gh_suggest_devices")
+	}
+	out := make([]int, n)
+	for i, d := range devs {
+		out[i] = int(d)
+	}
+	return out, float64(gbs), nil
+}

@@ -66,6 +66,7 @@ _lib = None
 _VP, _U64, _INT, _SZ = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_size_t
 ABI = {
     "gh_config_from_env": (_INT, [ctypes.POINTER(Config), ctypes.POINTER(ctypes.c_int), _INT, ctypes.POINTER(_INT)]),
+    "gh_suggest_devices": (_INT, [_INT, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_double)]),
     "gh_create": (_INT, [ctypes.POINTER(_VP), ctypes.POINTER(Config)]),
     "gh_destroy": (None, [_VP]),
     "gh_strerror": (ctypes.c_char_p, [_INT]),
@@ -174,6 +175,15 @@ def config_from_env():
         raise GpuHashError(rc, "gh_config_from_env")
     return ([devs[i] for i in range(cfg.n_devices)] if cfg.n_devices else None, int(cfg.slot_bytes), int(cfg.slots),
             int(cfg.stage_threads), bool(dis.value))
+
+
+def suggest_devices(n):
+    """gh_suggest_devices -> (list of n CUDA ordinals, aggregate host->device GB/s measured for them)."""
+    devs, gbs = (ctypes.c_int * max(n, 1))(), ctypes.c_double()
+    rc = load().gh_suggest_devices(n, devs, ctypes.byref(gbs))
+    if rc:
+        raise GpuHashError(rc, "gh_suggest_devices(%d)" % n)
+    return [devs[i] for i in range(n)], float(gbs.value)
 
 
 def last_kernel():

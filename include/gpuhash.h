@@ -90,6 +90,16 @@ typedef struct {
  * the stock crypto/sha1 / crypto/md5 paths in place. Host-only; needs no device. */
 int gh_config_from_env(gh_config* cfg, int* devices_buf, int devices_cap, int* disabled);
 
+/* Which n of the visible devices to give a context (no reference counterpart; the reference has no
+ * devices). The path is bound by the host->device link end to end, and GPUs that share a PCIe uplink
+ * share its bandwidth, so the choice is measured: pinned cudaMemcpyAsync on all devices of a candidate
+ * set at once (~0.4 s per candidate), for the first n devices and, when at least 2n are visible, for
+ * an evenly strided set; the plain first-n choice stays unless the other is clearly (3 %) better.
+ * devices_out receives n ordinals for gh_config.devices / GPUHASH_DEVICES; h2d_gbs_out (optional) the
+ * aggregate GB/s measured for them. Allocates 128 MiB of pinned and of device memory per probed device
+ * for the duration of the call. */
+int gh_suggest_devices(int n, int* devices_out, double* h2d_gbs_out);
+
 /* ---- lifecycle ---------------------------------------------------------------------------- */
 int         gh_create(gh_ctx** out, const gh_config* cfg /* NULL = defaults */);
 void        gh_destroy(gh_ctx* ctx);

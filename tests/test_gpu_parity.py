@@ -444,6 +444,26 @@ def test_incremental_stream_feed():
         ctx.close()
 
 
+def test_suggest_devices_returns_a_usable_set():
+    """gh_suggest_devices: n distinct visible ordinals and a measured link figure; a context over them works."""
+    torch = _torch()
+    count = torch.cuda.device_count()
+    for n in sorted({1, max(1, count // 2), count}):
+        devs, gbs = gpuhash.suggest_devices(n)
+        assert len(devs) == n and len(set(devs)) == n and all(0 <= d < count for d in devs)
+        assert gbs > 5.0  # a PCIe Gen3 x16 link does better than this
+    with pytest.raises(gpuhash.GpuHashError):
+        gpuhash.suggest_devices(count + 1)
+    devs, _ = gpuhash.suggest_devices(count)
+    ctx = gpuhash.Context(devices=devs)
+    try:
+        data = oracle.gen(3, 0, 200 * 16384)
+        got = ctx.HashParts([data], 16384, gpuhash.SHA1)[gpuhash.SHA1]
+        assert np.array_equal(got, oracle.hash_msgs(oracle.SHA1, data, 16384, 4))
+    finally:
+        ctx.close()
+
+
 def test_incremental_stream_feed_over_all_devices():
     """The same feed on a context over every visible device: windows go round the devices, digests
     and the bitmap are gathered from whichever device hashed a piece (one GPU: the degenerate case)."""
