@@ -30,6 +30,8 @@
 #include "../../include/gpuhash.h"
 #include "gh_internal.h"
 
+void gh_stage_copy(uint8_t* dst, const uint8_t* src, size_t n);  // gh_copy.cpp: non-temporal stores into the pinned mirror
+
 namespace {
 
 constexpr uint64_t kDefaultSlotBytes = 256ull << 20;
@@ -55,7 +57,7 @@ class Pool {
     void copy(uint8_t* dst, const uint8_t* src, uint64_t n) {
         const uint64_t grain = 2ull << 20;
         if (threads_.empty() || n <= grain) {
-            memcpy(dst, src, n);
+            gh_stage_copy(dst, src, n);
             return;
         }
         std::atomic<int> pending{0};
@@ -68,7 +70,7 @@ class Pool {
             const uint64_t len = std::min(each, n - off);
             std::lock_guard<std::mutex> g(mu_);
             q_.push_back([=, &pending, &dmu, &dcv] {
-                memcpy(dst + off, src + off, len);
+                gh_stage_copy(dst + off, src + off, len);
                 if (pending.fetch_sub(1) == 1) {
                     std::lock_guard<std::mutex> g2(dmu);
                     dcv.notify_one();
@@ -154,7 +156,7 @@ class Pool {
         const uint64_t nt = threads_.empty() ? 1 : threads_.size();
         const uint64_t per = std::max<uint64_t>(1, (rows + nt * 4 - 1) / (nt * 4));
         if (threads_.empty() || rows * width <= (2ull << 20)) {
-            for (uint64_t r = 0; r < rows; r++) memcpy(dst + r * dpitch, src + r * spitch, width);
+            for (uint64_t r = 0; r < rows; r++) gh_stage_copy(dst + r * dpitch, src + r * spitch, width);
             return;
         }
         std::atomic<int> pending{static_cast<int>((rows + per - 1) / per)};
@@ -164,7 +166,7 @@ class Pool {
             const uint64_t r1 = std::min(rows, r0 + per);
             std::lock_guard<std::mutex> g(mu_);
             q_.push_back([=, &pending, &dmu, &dcv] {
-                for (uint64_t r = r0; r < r1; r++) memcpy(dst + r * dpitch, src + r * spitch, width);
+                for (uint64_t r = r0; r < r1; r++) gh_stage_copy(dst + r * dpitch, src + r * spitch, width);
                 if (pending.fetch_sub(1) == 1) {
                     std::lock_guard<std::mutex> g2(dmu);
                     dcv.notify_one();

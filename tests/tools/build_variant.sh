@@ -9,5 +9,5 @@ NV="/usr/local/cuda/bin/nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a
 src=downloader-go_b200/csrc
 $NV "$@" -c -o build/obj_$name/gh_kernels.o $src/gh_kernels.cu
 [ -f $src/gh_api.o ] || make -s -C $src
-/usr/local/cuda/bin/nvcc -shared -gencode arch=compute_100a,code=sm_100a -o build/libgpuhash_$name.so build/obj_$name/gh_kernels.o $src/gh_api.o $src/gh_metainfo.o $src/gh_config.o -lpthread
+/usr/local/cuda/bin/nvcc -shared -gencode arch=compute_100a,code=sm_100a -o build/libgpuhash_$name.so build/obj_$name/gh_kernels.o $src/gh_api.o $src/gh_metainfo.o $src/gh_config.o $src/gh_copy.o -lpthread
 echo build/libgpuhash_$name.so
