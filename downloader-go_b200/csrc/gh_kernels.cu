@@ -676,27 +676,27 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 }
 
 // ---------------------------------------------------------------------------- trio hasher (SHA-1)
-// What the two kernels above leave on the table (measured on B200, profiles/r02_ab_team_trio.jsonl):
-// a warp that is alone on its sub-partition issues at ~0.6 IPC whatever it runs -- its own dependent
-// instructions are 4-5 clocks apart and nothing fills the gaps -- so neither the lane kernel (one
-// chain = one warp = 1 190 clk per 64-byte block at config 2) nor a rounds-warp fed by ONE schedule
-// warp (the schedule warp, alone on its sub-partition, needs ~490 clk per block and becomes the
-// bottleneck as soon as it serves more than one chain) gets near the ALU pipes' capacity. The pipes
-// only fill when every sub-partition holds two or three warps with independent work.
+// What the two kernels above leave on the table (measured on B200: profiles/r02_ab_sha1_kernels.jsonl,
+// profiles/r02_ab_team_kernel_rejected.jsonl): a warp that is alone on its sub-partition issues at
+// 0.45-0.7 IPC whatever it runs -- its own dependent instructions are 4-5 clocks apart and nothing
+// fills the gaps -- so neither the lane kernel (one chain = one warp = 1 185 clk per 64-byte block at
+// config 2) nor a rounds-warp fed by ONE schedule warp (which, alone on its sub-partition, needs ~490
+// clk per block and is the bottleneck as soon as it serves more than one chain) gets near the ALU
+// pipes' capacity.
 //
 // The schedule of block b does not depend on block b-1, so one chain can feed on SEVERAL schedule
 // warps. Here a chain (32 messages) is served by three warps:
 //   R    rounds: owns the chaining state, reads W+K from shared memory, runs only the 80 rounds;
-//   S_a  schedule of the even hand-off batches (TMA tiles -> byte swap -> W[0..79] + K -> shared memory);
-//   S_b  schedule of the odd ones.
-// and a CTA carries up to three chains: nine working warps on the four sub-partitions of one SM. With
-// warp w on sub-partition w % 4 the roles are laid out so that sub-partitions 0-2 each hold one R and
-// one S warp (R has the higher warp id: the issue arbiter prefers it, and R is the serial chain) and
-// sub-partition 3 holds the three remaining S warps: ~486 + 232 ALU-pipe issue clocks per block on
-// 0-2, 3 x 232 on 3 -- the same ~710 everywhere, against 944 for one whole block on one pipe.
-// Every (chain, buffer) has exactly one producer warp and one consumer warp, so the full/empty
-// mbarrier pairs never have two waiters a phase apart; each S warp owns the two TMA stages of its
-// batch parity and is their only reader, so the tile ring needs no "empty" barrier.
+//   S_a  schedule (TMA tiles -> byte swap -> W[0..79] + K -> shared memory) of RATIO of every RATIO+1
+//        hand-off batches;
+//   S_b  schedule of the remaining one.
+// A CTA carries one chain (three warps on three sub-partitions) or three: nine working warps on the
+// four sub-partitions of one SM. With warp w on sub-partition w % 4 the roles are laid out so that
+// sub-partitions 0-2 each hold one R and its chain's S_b and sub-partition 3 holds the three S_a
+// warps; RATIO = 2 evens the ALU issue load out (R 650 + S_b 142 clocks per block-step against
+// 3 x 284). Every (chain, buffer) has exactly one producer warp and one consumer warp, so the
+// full/empty mbarrier pairs never have two waiters a phase apart; every TMA stage belongs to one
+// S warp, its only reader, so the tile ring needs no "empty" barrier.
 #ifndef GH_TRIO_RATIO3
 #define GH_TRIO_RATIO3 2  // S_a : S_b share in the three-chains-per-CTA layout (2:1 measured +5 % over 1:1 at config 2)
 #endif
