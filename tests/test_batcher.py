@@ -180,3 +180,28 @@ def test_batches_larger_than_64_pieces_shard_over_all_devices():
     b.close()
     ctx.close()
     assert torch.cuda.device_count() >= 1
+
+
+def test_batch_larger_than_a_ring_slot_runs_chunk_interleaved():
+    """40 pieces of 8 MiB (one of them short) in one batch: 320 MiB against 256 MiB ring slots, so the
+    batch takes the chunk-interleaved windows with a per-piece length table."""
+    ctx = gpuhash.Context(devices=[0])
+    n, L, last = 40, 8 << 20, (3 << 20) + 77
+    data, expected, total = _payload(67, n, L, last)
+    dirty = data.copy()
+    dirty[17 * L + 12345] ^= 1
+    b = ctx.Batcher(L, n, 60000)
+    res = [None] * n
+
+    def one(i):
+        res[i] = b.verify(dirty[i * L: min((i + 1) * L, total)], expected[i], want_digest=True)
+
+    order = list(range(n))[::-1]  # the short last piece arrives first
+    ts = [threading.Thread(target=one, args=(i,)) for i in order]
+    [t.start() for t in ts]
+    [t.join(timeout=120) for t in ts]
+    want = oracle.hash_msgs(oracle.SHA1, dirty, L, 4)
+    assert [i for i in range(n) if not res[i][0]] == [17]
+    assert all(res[i][1] == want[i].tobytes() for i in range(n))
+    b.close()
+    ctx.close()
