@@ -372,6 +372,9 @@ gh_hash_lanes(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 #ifndef GH_HANDOFF
 #define GH_HANDOFF 4
 #endif
+#ifndef GH_SPLIT_R_PAIRS
+#define GH_SPLIT_R_PAIRS 1
+#endif
 #ifndef GH_R_IADD3
 #define GH_R_IADD3 1  // SHA-1 rounds warps: f + e + WK as one IADD3 (see sha1_rounds); 0 = the two-IMAD form
 #endif
@@ -652,6 +655,15 @@ gh_hash_split(const __grid_constant__ CUtensorMap tmap, const GhJob job) {
 #pragma unroll 1
             for (uint32_t half = 0; half < kHandoff && jb + half < n_blocks; half++) {
                 const uint32_t wk_addr = wk_u32 + (wb * kHandoff + half) * Cfg::kWkBytes + lane * 16;
+                if constexpr (ALGO == GH_SHA1 && GH_SPLIT_R_PAIRS) {
+                    // two blocks as one unrolled body, WK prefetch rolling across the boundary (the rounds
+                    // warp has its sub-partition to itself here; see gh_hash_trio<1, true>)
+                    if (job.lens == nullptr && jb + half + 2 <= n_blocks && half + 2 <= kHandoff) {
+                        sha1_rounds_n<2>(L.s1, wk_addr);
+                        half++;
+                        continue;
+                    }
+                }
                 if (jb + half < my_blocks) {
                     if constexpr (ALGO == GH_SHA1) sha1_rounds(L.s1, wk_addr, job.one);
                     else sha256_rounds(L.s2, wk_addr, job.one);
