@@ -74,3 +74,20 @@ extern "C" int gh_config_from_env(gh_config* cfg, int* devices_buf, int devices_
     }
     return GH_OK;
 }
+
+// Lowercase hex of n digests of digest_len bytes each, in order, 2*digest_len characters per digest, no
+// separators, NUL after the last: the form SigV4 wants (X-Amz-Content-Sha256, and the per-chunk
+// string-to-sign of the streaming signature, which chains chunk k's signature on hex(sha256(chunk k))).
+extern "C" int gh_hex_digests(const uint8_t* digests, uint64_t n, int digest_len, char* out, size_t out_len) {
+    if (!out || digest_len <= 0 || (n && !digests)) return GH_EINVAL;
+    const uint64_t need = n * 2ull * static_cast<uint64_t>(digest_len) + 1;
+    if (out_len < need) return GH_ERANGE;
+    static const char kHex[] = "0123456789abcdef";
+    const uint64_t bytes = n * static_cast<uint64_t>(digest_len);
+    for (uint64_t i = 0; i < bytes; i++) {
+        out[2 * i] = kHex[digests[i] >> 4];
+        out[2 * i + 1] = kHex[digests[i] & 15];
+    }
+    out[2 * bytes] = 0;
+    return GH_OK;
+}

@@ -78,6 +78,7 @@ ABI = {
     "gh_debug_fail_nth_copy": (_INT, [_VP, ctypes.c_int64]),
     "gh_verify_pieces": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_hash_parts": (_INT, [_VP, ctypes.POINTER(Span), _SZ, _U64, _INT, _VP, _VP, _VP]),
+    "gh_hex_digests": (_INT, [_VP, _U64, _INT, ctypes.c_char_p, _SZ]),
     "gh_s3_etag": (_INT, [_VP, _VP, _U64, ctypes.c_char_p, _SZ]),
     "gh_verify_files": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _VP, _VP, _VP, ctypes.POINTER(_U64)]),
     "gh_hash_file_parts": (_INT, [_VP, ctypes.POINTER(File), _SZ, _U64, _INT, _VP, _VP, _VP]),
@@ -184,6 +185,18 @@ def suggest_devices(n):
     if rc:
         raise GpuHashError(rc, "gh_suggest_devices(%d)" % n)
     return [devs[i] for i in range(n)], float(gbs.value)
+
+
+def hex_digests(digests):
+    """[n, digest_len] uint8 -> list of n lowercase hex strings (gh_hex_digests), chunk order kept."""
+    a = np.ascontiguousarray(digests, dtype=np.uint8)
+    n, dl = a.shape
+    buf = ctypes.create_string_buffer(n * 2 * dl + 1)
+    rc = load().gh_hex_digests(_ptr(a) if n else None, n, dl, buf, len(buf))
+    if rc:
+        raise GpuHashError(rc, "gh_hex_digests")
+    txt = buf.value.decode()
+    return [txt[2 * dl * i:2 * dl * (i + 1)] for i in range(n)]
 
 
 def last_kernel():

@@ -277,6 +277,12 @@ int gh_hash_file_parts_per_file(gh_ctx* ctx, const gh_file* files, size_t n_file
  * out needs at least 56 bytes. */
 int gh_s3_etag(gh_ctx* ctx, const uint8_t* part_md5s, uint64_t n_parts, char* out, size_t out_len);
 
+/* Lowercase hex of n digests (digest_len bytes each) in order, 2*digest_len characters per digest, no
+ * separators, NUL-terminated: the form minio-go's signer uses for X-Amz-Content-Sha256 and, per 64 KiB
+ * chunk, in the streaming-SigV4 string-to-sign that the reference's plain-HTTP uploads produce
+ * (uploader.go:32-35, :89). out_len >= n*2*digest_len + 1, else GH_ERANGE. Host-only. */
+int gh_hex_digests(const uint8_t* digests, uint64_t n, int digest_len, char* out, size_t out_len);
+
 /* ---- device-resident entry points (payload already in HBM; "kernel-only" numbers) ------------ */
 
 /* Same contract as gh_verify_pieces / gh_hash_parts but every pointer is a DEVICE pointer on

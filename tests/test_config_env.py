@@ -78,3 +78,16 @@ def test_c_caller_sees_the_same(env, tmp_path):
     out = subprocess.run([exe], env=dict(os.environ, GPUHASH_DEVICES="1,5", GPUHASH_SLOT_MIB="32", GPUHASH_SLOTS="3",
                                          GPUHASH_DISABLE="1"), capture_output=True, text=True).stdout.split()
     assert out == ["0", "2", "5", str(32 << 20), "3", "0", "1"]
+
+
+def test_hex_digests_for_the_signer():
+    """gh_hex_digests: lowercase hex, chunk order, what X-Amz-Content-Sha256 / the chunk string-to-sign take."""
+    import hashlib
+    import ctypes
+    import numpy as np
+    chunks = [bytes([i]) * (100 + i) for i in range(5)]
+    dig = np.array([list(hashlib.sha256(c).digest()) for c in chunks], dtype=np.uint8)
+    assert gpuhash.hex_digests(dig) == [hashlib.sha256(c).hexdigest() for c in chunks]
+    assert gpuhash.hex_digests(np.zeros((0, 32), dtype=np.uint8)) == []
+    buf = ctypes.create_string_buffer(10)
+    assert gpuhash.load().gh_hex_digests(ctypes.c_void_p(dig.ctypes.data), 5, 32, buf, 10) == gpuhash.GH_ERANGE
