@@ -205,3 +205,54 @@ def test_batch_larger_than_a_ring_slot_runs_chunk_interleaved():
     assert all(res[i][1] == want[i].tobytes() for i in range(n))
     b.close()
     ctx.close()
+
+
+def test_randomised_stress_small_batches_cancellations_and_short_deadline():
+    """Sixteen threads, 2 400 pieces of random length (0 .. L bytes), an 8-piece batch limit and a 3 ms
+    deadline, random pauses, one reservation in twenty given back: thousands of small batches and
+    every hand-over between the filling and the in-flight buffer; each verdict against hashlib."""
+    import hashlib
+    import random
+    ctx = gpuhash.Context(devices=[0])
+    L = 40000
+    b = ctx.Batcher(L, 8, 3)
+    src = oracle.gen(68, 0, 4 << 20)
+    errors, done = [], [0] * 16
+
+    def worker(w):
+        rnd = random.Random(1000 + w)
+        try:
+            for k in range(150):
+                n = rnd.choice((0, 1, 55, 64, 4096, L, rnd.randrange(L + 1)))
+                off = rnd.randrange(src.size - L)
+                piece = src[off:off + n]
+                want = hashlib.sha1(piece.tobytes()).digest()
+                corrupt = rnd.random() < 0.1
+                exp = bytes([want[0] ^ 1]) + want[1:] if corrupt else want
+                if rnd.random() < 0.05:
+                    slot, view = b.reserve(n)
+                    time.sleep(rnd.random() * 0.002)
+                    assert b.cancel(slot) == 0
+                    continue
+                if rnd.random() < 0.5:
+                    slot, view = b.reserve(n)
+                    view[:] = piece
+                    if rnd.random() < 0.3:
+                        time.sleep(rnd.random() * 0.004)  # a slow producer: the batch must wait for its commit
+                    ok = b.commit(slot, exp)
+                else:
+                    ok, dig = b.verify(piece, exp, want_digest=True)
+                    assert dig == want
+                assert ok is (not corrupt), (w, k, n)
+                done[w] += 1
+        except Exception as e:  # noqa
+            errors.append((w, repr(e)))
+
+    ts = [threading.Thread(target=worker, args=(w,)) for w in range(16)]
+    [t.start() for t in ts]
+    [t.join(timeout=300) for t in ts]
+    st = b.stats()
+    b.close()
+    ctx.close()
+    assert not errors, errors[:3]
+    assert sum(done) > 2000 and st.failed_batches == 0 and st.pieces >= sum(done)
