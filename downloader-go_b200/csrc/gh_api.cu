@@ -34,6 +34,23 @@ void gh_stage_copy(uint8_t* dst, const uint8_t* src, size_t n);  // gh_copy.cpp:
 
 namespace {
 
+// The library makes the device it needs current on every entry (goroutines migrate between OS
+// threads), but it gives the calling thread its own current device back on the way out: a caller
+// that shares the CUDA runtime with the library (PyTorch in the tests and bench.py, any C++ host)
+// must not find its allocations landing on another GPU after a gh_* call.
+struct DeviceRestore {
+    int prev = -1;
+    DeviceRestore() {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            prev = -1;
+            cudaGetLastError();
+        }
+    }
+    ~DeviceRestore() {
+        if (prev >= 0 && cudaSetDevice(prev) != cudaSuccess) cudaGetLastError();
+    }
+};
+
 constexpr uint64_t kDefaultSlotBytes = 256ull << 20;
 constexpr int kDefaultSlots = 4;
 constexpr int kDefaultStageThreads = 4;
@@ -859,6 +876,7 @@ int run_table(gh_ctx* c, SpanIndex& ix, const MsgTable& T, int algos, const uint
 int run_batch(gh_ctx* c, const gh_span* spans, size_t n_spans, uint64_t msg_len, int algos, const uint8_t* expected,
               uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad,
               bool per_file = false) {
+    DeviceRestore restore_device;
     if (!c) return GH_EINVAL;
     std::lock_guard<std::mutex> g(c->mu);
     if (n_spans && !spans) return fail(c, GH_EINVAL, "spans is NULL");
@@ -872,6 +890,7 @@ int run_batch(gh_ctx* c, const gh_span* spans, size_t n_spans, uint64_t msg_len,
 int run_files(gh_ctx* c, const gh_file* files, size_t n_files, uint64_t msg_len, int algos, const uint8_t* expected,
               uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* bitmap, uint64_t* n_bad,
               bool per_file = false) {
+    DeviceRestore restore_device;
     if (!c) return GH_EINVAL;
     std::lock_guard<std::mutex> g(c->mu);
     if (n_files && !files) return fail(c, GH_EINVAL, "files is NULL");
@@ -1020,6 +1039,7 @@ void gh_shard_range(uint64_t n_msgs, int n_shards, int shard, uint64_t* begin, u
 }
 
 int gh_create(gh_ctx** out, const gh_config* cfg) {
+    DeviceRestore restore_device;
     if (!out) return GH_EINVAL;
     *out = nullptr;
     int count = 0;
@@ -1068,6 +1088,7 @@ int gh_create(gh_ctx** out, const gh_config* cfg) {
 }
 
 void gh_destroy(gh_ctx* c) {
+    DeviceRestore restore_device;
     if (!c) return;
     for (auto& d : c->devs) {
         if (cudaSetDevice(d.ordinal) != cudaSuccess) continue;
@@ -1184,6 +1205,7 @@ static void stream_drain_all(gh_ctx* c) {
 
 int gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len, const uint8_t* expected,
                    gh_stream** out) {
+    DeviceRestore restore_device;
     if (!ctx || !out) return GH_EINVAL;
     *out = nullptr;
     std::lock_guard<std::mutex> g(ctx->mu);
@@ -1238,6 +1260,7 @@ int gh_stream_open(gh_ctx* ctx, int algos, uint64_t msg_len, uint64_t total_len,
 }
 
 int gh_stream_acquire(gh_stream* st, void** buf, uint64_t* cap) {
+    DeviceRestore restore_device;
     if (!st || !buf || !cap) return GH_EINVAL;
     gh_ctx* c = st->c;
     std::lock_guard<std::mutex> g(c->mu);
@@ -1265,6 +1288,7 @@ int gh_stream_acquire(gh_stream* st, void** buf, uint64_t* cap) {
 }
 
 int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
+    DeviceRestore restore_device;
     if (!st) return GH_EINVAL;
     gh_ctx* c = st->c;
     std::lock_guard<std::mutex> g(c->mu);
@@ -1317,6 +1341,7 @@ int gh_stream_submit(gh_stream* st, uint64_t n_bytes) {
 
 int gh_stream_finish(gh_stream* st, uint8_t* sha1_out, uint8_t* md5_out, uint8_t* sha256_out, uint64_t* ok_bitmap_out,
                      uint64_t* n_bad_out) {
+    DeviceRestore restore_device;
     if (!st) return GH_EINVAL;
     gh_ctx* c = st->c;
     int rc = GH_OK;
@@ -1379,6 +1404,7 @@ int gh_stream_finish(gh_stream* st, uint8_t* sha1_out, uint8_t* md5_out, uint8_t
 }
 
 void gh_stream_abort(gh_stream* st) {
+    DeviceRestore restore_device;
     if (!st) return;
     gh_ctx* c = st->c;
     {
@@ -1651,6 +1677,7 @@ void gh_batcher_destroy(gh_batcher* B) {
 
 // ---- device-resident -----------------------------------------------------------------------
 static int device_call(gh_ctx* ctx, int dev_index, int algos, const GhJob& job_in, void* cuda_stream) {
+    DeviceRestore restore_device;
     Device* d = get_dev(ctx, dev_index);
     if (!d) return fail(ctx, GH_EINVAL, "bad device index");
     std::lock_guard<std::mutex> g(ctx->mu);
@@ -1743,6 +1770,7 @@ int gh_hash_update_device(gh_ctx* ctx, int dev_index, int algos, const void* d_d
 
 int gh_generate_device(gh_ctx* ctx, int dev_index, void* d_out, uint64_t seed, uint64_t offset, uint64_t len,
                        void* cuda_stream) {
+    DeviceRestore restore_device;
     Device* d = get_dev(ctx, dev_index);
     if (!d) return fail(ctx, GH_EINVAL, "bad device index");
     if (len && !d_out) return fail(ctx, GH_EINVAL, "d_out is NULL");
@@ -1852,6 +1880,7 @@ int gh_host_register(void* p, size_t bytes) {
 int gh_host_unregister(void* p) { return cudaHostUnregister(p) == cudaSuccess ? GH_OK : GH_ECUDA; }
 
 int gh_device_alloc(gh_ctx* ctx, int dev_index, void** out, size_t bytes) {
+    DeviceRestore restore_device;
     Device* d = get_dev(ctx, dev_index);
     if (!d || !out) return GH_EINVAL;
     GH_CUDA(ctx, cudaSetDevice(d->ordinal));
@@ -1859,6 +1888,7 @@ int gh_device_alloc(gh_ctx* ctx, int dev_index, void** out, size_t bytes) {
     return GH_OK;
 }
 int gh_device_free(gh_ctx* ctx, int dev_index, void* p) {
+    DeviceRestore restore_device;
     Device* d = get_dev(ctx, dev_index);
     if (!d) return GH_EINVAL;
     GH_CUDA(ctx, cudaSetDevice(d->ordinal));
@@ -1866,6 +1896,7 @@ int gh_device_free(gh_ctx* ctx, int dev_index, void* p) {
     return GH_OK;
 }
 int gh_memcpy_d2h(gh_ctx* ctx, int dev_index, void* dst_host, const void* src_dev, size_t bytes) {
+    DeviceRestore restore_device;
     Device* d = get_dev(ctx, dev_index);
     if (!d) return GH_EINVAL;
     GH_CUDA(ctx, cudaSetDevice(d->ordinal));
@@ -1873,6 +1904,7 @@ int gh_memcpy_d2h(gh_ctx* ctx, int dev_index, void* dst_host, const void* src_de
     return GH_OK;
 }
 int gh_memcpy_h2d(gh_ctx* ctx, int dev_index, void* dst_dev, const void* src_host, size_t bytes) {
+    DeviceRestore restore_device;
     Device* d = get_dev(ctx, dev_index);
     if (!d) return GH_EINVAL;
     GH_CUDA(ctx, cudaSetDevice(d->ordinal));

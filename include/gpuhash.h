@@ -18,7 +18,9 @@
  *     caller pointer after returning (the cgo pointer rule). Long-lived memory (staging ring,
  *     midstates) is allocated by the library.
  *   - a gh_ctx may be used from several OS threads; calls are serialised per context. The library
- *     calls cudaSetDevice itself on entry (goroutines migrate between OS threads).
+ *     calls cudaSetDevice itself on entry (goroutines migrate between OS threads) and gives the
+ *     calling thread its previous current device back on return, so a host that shares the CUDA
+ *     runtime with the library is not moved to another GPU by a gh_* call.
  *   - there is NO CPU fallback: without a usable CUDA device gh_create fails with GH_ENODEVICE.
  *   - digests are raw bytes in the standard byte order (what Go's hash.Hash.Sum returns).
  *   - bitmaps: bit (i & 63) of word (i >> 6) is 1 iff piece i matched its expected SHA-1.

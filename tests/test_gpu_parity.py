@@ -444,6 +444,29 @@ def test_incremental_stream_feed():
         ctx.close()
 
 
+def test_calls_leave_the_callers_current_device_alone():
+    """A context over every device touches every device, yet the calling thread's current device is
+    what it was afterwards (a host sharing the CUDA runtime -- torch here -- keeps allocating where it
+    did before)."""
+    torch = _torch()
+    last = torch.cuda.device_count() - 1
+    for cur in sorted({0, last}):
+        torch.cuda.set_device(cur)
+        ctx = gpuhash.Context()
+        try:
+            assert torch.cuda.current_device() == cur
+            data = oracle.gen(4, 0, 300 * 4096)
+            ctx.HashParts([data], 4096, gpuhash.SHA1 | gpuhash.MD5)
+            st = ctx.Stream(gpuhash.SHA1, 4096, 8192)
+            st.abort()
+            t = torch.zeros(16, device="cuda")
+            assert t.device.index == cur and torch.cuda.current_device() == cur
+        finally:
+            ctx.close()
+        assert torch.cuda.current_device() == cur
+    torch.cuda.set_device(0)
+
+
 def test_suggest_devices_returns_a_usable_set():
     """gh_suggest_devices: n distinct visible ordinals and a measured link figure; a context over them works."""
     torch = _torch()
